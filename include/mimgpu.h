@@ -1,0 +1,272 @@
+/*
+ * mimgpu.h -- C ABI of the B200-native batched OCP-QP engine.
+ *
+ * This is the drop-in boundary for the `computeDirection` hot path of
+ * mim_solvers' SolverSQP / SolverCSQP / SolverFDDP, for a batch of B independent
+ * shooting problems of one shape (T, nx, nu, ng, ngT).  The reference has no
+ * FFI layer: its seam is C++ virtual dispatch on crocoddyl::SolverAbstract
+ * subclasses.  Each entry point below names the reference member function(s) it
+ * replaces (paths relative to the reference tree).
+ *
+ * Conventions
+ *   - extern "C", plain pointers and sizes, all reals are IEEE binary64, all
+ *     sizes int32; every function returns an int status (MIMGPU_OK == 0) and
+ *     never throws.
+ *   - Matrices are dense COLUMN-MAJOR blocks, i.e. the memory image of the
+ *     Eigen::MatrixXd members of crocoddyl::ActionDataAbstract (d->Fx, d->Fu,
+ *     d->Lxx, ...), so an adapter packs them with memcpy.  The only row-major
+ *     block is the feedback gain K (nu x nx), as in the reference
+ *     (include/mim_solvers/ddp.hpp:69-70,397).
+ *   - Batch layout ("problem-major SoA"): one array per field, shaped
+ *     [B][T][block] (running knots) or [B][block] (terminal knot), contiguous.
+ *     `nx` is the tangent dimension ndx (src/ddp.cpp:467).
+ *   - A ctx is bound to one device and one shape bucket; it owns all device
+ *     buffers and the persistent per-problem ADMM state (y, z, rho_vec,
+ *     rho_sparse, dx, du), mirroring the solver-object members of
+ *     include/mim_solvers/csqp.hpp:250-357.  One host thread at a time per ctx.
+ *     All device work is enqueued on the caller's stream.
+ *   - Numerical failure is reported per problem in `status[b]` (the reference
+ *     throws "backward_error": src/ddp.cpp:340-345,415-419), never by a
+ *     non-zero return code.
+ */
+#ifndef MIMGPU_H_
+#define MIMGPU_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MIMGPU_ABI_VERSION 1
+
+/* ---- return codes ------------------------------------------------------ */
+#define MIMGPU_OK 0
+#define MIMGPU_ERR_INVALID 1   /* bad argument / shape            */
+#define MIMGPU_ERR_CUDA 2      /* CUDA runtime error (see mimgpu_last_error) */
+#define MIMGPU_ERR_NODEVICE 3  /* no CUDA device: there is no CPU fallback */
+#define MIMGPU_ERR_STATE 4     /* call order (e.g. direction before upload) */
+#define MIMGPU_ERR_UNSUPPORTED 5
+
+/* ---- per-problem status word (status[b]) --------------------------------
+ * 0 ok; 1 = Quu not positive definite at some knot (Eigen LLT info != Success,
+ * src/ddp.cpp:413-419); 2 = non-finite / >=1e30 Vx or Vxx (raiseIfNaN,
+ * src/ddp.cpp:340-345).  Bits 8.. hold the knot index t of the first failure. */
+#define MIMGPU_STATUS_OK 0
+#define MIMGPU_STATUS_LLT 1
+#define MIMGPU_STATUS_NONFINITE 2
+
+typedef struct mimgpu_ctx mimgpu_ctx; /* opaque */
+
+typedef struct {
+  int32_t B;   /* problems in this ctx (this rank's shard)            */
+  int32_t T;   /* running knots; there are T+1 states                  */
+  int32_t nx;  /* tangent-space dimension ndx                          */
+  int32_t nu;  /* controls (same at every running knot)                */
+  int32_t ng;  /* inequality rows per running knot (0 = none)          */
+  int32_t ngT; /* inequality rows at the terminal knot (0 = none)      */
+} mimgpu_shape;
+
+/* Per-knot derivatives, as produced by problem_->calcDiff (src/ddp.cpp:258,
+ * src/csqp.cpp:413-414).  Host or device pointers (see mimgpu_upload). CSQP
+ * pointers may be NULL when ng == 0 / ngT == 0. */
+typedef struct {
+  const double* Fx;   /* [B][T][nx*nx]  d->Fx  (col-major nx x nx)   */
+  const double* Fu;   /* [B][T][nx*nu]  d->Fu  (nx x nu)             */
+  const double* Lxx;  /* [B][T][nx*nx]                                 */
+  const double* Lxu;  /* [B][T][nx*nu]  (nx x nu)                     */
+  const double* Luu;  /* [B][T][nu*nu]                                 */
+  const double* Lx;   /* [B][T][nx]                                    */
+  const double* Lu;   /* [B][T][nu]                                    */
+  const double* fs;   /* [B][T+1][nx]   gaps fs_[0..T]; fs_[t+1] is the
+                         defect of knot t (src/csqp.cpp:431)           */
+  const double* LxxT; /* [B][nx*nx]     terminal d_T->Lxx              */
+  const double* LxT;  /* [B][nx]        terminal d_T->Lx               */
+  const double* Gx;   /* [B][T][ng*nx]  d->Gx  (ng x nx)              */
+  const double* Gu;   /* [B][T][ng*nu]  d->Gu  (ng x nu)              */
+  const double* g;    /* [B][T][ng]     d->g                           */
+  const double* g_lb; /* [B][T][ng]     m->get_g_lb()  (+-inf allowed) */
+  const double* g_ub; /* [B][T][ng]     m->get_g_ub()                  */
+  const double* GxT;  /* [B][ngT*nx]                                   */
+  const double* gT;   /* [B][ngT]                                      */
+  const double* g_lbT;/* [B][ngT]                                      */
+  const double* g_ubT;/* [B][ngT]                                      */
+  const double* cost; /* [B]            cost_ (may be NULL -> 0)       */
+} mimgpu_derivs;
+
+#define MIMGPU_MEM_HOST 0   /* pointers are host memory: async H2D copy      */
+#define MIMGPU_MEM_DEVICE 1 /* pointers are device memory in the layout above:
+                               attached zero-copy, caller keeps them alive    */
+
+/* SolverSQP / SolverFDDP direction parameters (src/sqp.cpp:91-97,224-242). */
+typedef struct {
+  double preg;        /* preg_  (NaN = skip, src/ddp.cpp:271)          */
+  double dreg;        /* dreg_                                          */
+  double mu_dynamic;  /* merit_ = cost_ + mu_dynamic_*gap_norm_         */
+  int32_t is_feasible;/* SQP forces 0 (src/sqp.cpp:85)                  */
+  int32_t reserved;
+} mimgpu_sqp_params;
+
+/* SolverCSQP QP parameters; defaults in include/mim_solvers/csqp.hpp:292-331 */
+typedef struct {
+  double preg, dreg;              /* 0 when remove_reg_ (src/csqp.cpp:216-219) */
+  double sigma;                   /* 1e-6 */
+  double alpha;                   /* 1.6  */
+  double rho_sparse_base;         /* 1e-1 */
+  double rho_min, rho_max;        /* 1e-6, 1e3 */
+  double adaptive_rho_tolerance;  /* 5 */
+  double eps_abs, eps_rel;        /* 1e-4, 1e-4 */
+  int32_t max_qp_iters;           /* 1000 */
+  int32_t rho_update_interval;    /* 25 */
+  int32_t equality_qp_initial_guess; /* 1 */
+  int32_t reset_y;                /* 0 */
+  int32_t reset_rho;              /* 0 */
+  int32_t update_rho_with_heuristic; /* 0 */
+  int32_t warm_start_y;           /* unused, reserved (0) */
+  int32_t reserved;
+} mimgpu_csqp_params;
+
+/* Downloadable / uploadable per-problem fields (solver members). */
+enum mimgpu_field {
+  MIMGPU_F_DX = 0,        /* dx_        [B][T+1][nx]  (SQP: direction; CSQP: prox centre) */
+  MIMGPU_F_DU = 1,        /* du_        [B][T][nu]    */
+  MIMGPU_F_LAG_MUL = 2,   /* lag_mul_   [B][T+1][nx]  */
+  MIMGPU_F_DX_TILDE = 3,  /* dxtilde_   [B][T+1][nx]  */
+  MIMGPU_F_DU_TILDE = 4,  /* dutilde_   [B][T][nu]    */
+  MIMGPU_F_Y = 5,         /* y_         [B][T*ng+ngT] */
+  MIMGPU_F_Z = 6,         /* z_         [B][T*ng+ngT] */
+  MIMGPU_F_RHO_VEC = 7,   /* rho_vec_   [B][T*ng+ngT] */
+  MIMGPU_F_VXX = 8,       /* Vxx_       [B][T+1][nx*nx] */
+  MIMGPU_F_VX = 9,        /* Vx_        [B][T+1][nx]  */
+  MIMGPU_F_K = 10,        /* K_         [B][T][nu*nx] row-major nu x nx */
+  MIMGPU_F_KFF = 11,      /* k_         [B][T][nu]    */
+  MIMGPU_F_QU = 12,       /* Qu_        [B][T][nu]    */
+  MIMGPU_F_QUUK = 13,     /* Quuk_      [B][T][nu]    (SQP/FDDP only) */
+  MIMGPU_F_QUU_LLT = 14,  /* lower Cholesky factor of Quu_ [B][T][nu*nu] col-major */
+  MIMGPU_F_COUNT = 15
+};
+
+/* Per-problem scalars ([B] each). */
+enum mimgpu_scalar {
+  MIMGPU_S_KKT = 0,
+  MIMGPU_S_GAP_NORM = 1,
+  MIMGPU_S_MERIT = 2,          /* SQP only: cost_ + mu_dynamic_*gap_norm_ */
+  MIMGPU_S_XGRAD_NORM = 3,
+  MIMGPU_S_UGRAD_NORM = 4,
+  MIMGPU_S_NORM_PRIMAL = 5,
+  MIMGPU_S_NORM_DUAL = 6,
+  MIMGPU_S_NORM_PRIMAL_REL = 7,
+  MIMGPU_S_NORM_DUAL_REL = 8,
+  MIMGPU_S_RHO_SPARSE = 9,
+  MIMGPU_S_CONSTRAINT_NORM = 10,
+  MIMGPU_S_DG = 11,            /* FDDP dg_ (src/fddp.cpp:256-279) */
+  MIMGPU_S_DQ = 12,            /* FDDP dq_ */
+  MIMGPU_S_COUNT = 13
+};
+
+/* Batch-wide summary (the quantities of SURVEY 8(e) all-reduce). */
+typedef struct {
+  double max_kkt;
+  int64_t sum_qp_iters;
+  int64_t max_qp_iters;
+  int64_t n_converged;  /* CSQP: problems whose ADMM loop broke on tolerance */
+  int64_t n_failed;     /* status != 0 */
+} mimgpu_summary;
+
+/* ---- lifecycle ----------------------------------------------------------- */
+int mimgpu_abi_version(void);
+int mimgpu_device_count(int* n);
+const char* mimgpu_last_error(void);
+
+/* Allocates all device buffers for `shape` on `device`.  Replaces
+ * SolverDDP::allocateData (src/ddp.cpp:447-502) and the SolverCSQP ctor
+ * allocations (src/csqp.cpp:24-168): dx, du, dxtilde, dutilde, lag_mul, y, z
+ * are zero-initialised exactly as there. */
+int mimgpu_create(mimgpu_ctx** out, int device, const mimgpu_shape* shape);
+void mimgpu_destroy(mimgpu_ctx* ctx);
+int mimgpu_get_shape(const mimgpu_ctx* ctx, mimgpu_shape* shape);
+
+/* ---- data in ------------------------------------------------------------- */
+/* Makes the derivatives of all B problems visible to the kernels; the upload
+ * point is right after problem_->calcDiff (src/ddp.cpp:253-263,
+ * src/csqp.cpp:411-416).  MIMGPU_MEM_HOST: cudaMemcpyAsync on `stream` (pin
+ * the host memory for overlap).  MIMGPU_MEM_DEVICE: pointers attached. */
+int mimgpu_upload(mimgpu_ctx* ctx, const mimgpu_derivs* derivs, int memkind,
+                  void* cuda_stream);
+
+/* Per-problem regularisation (solver members preg_/dreg_, src/ddp.cpp:431-445)
+ * for batches whose problems are at different regularisation levels.  NULL
+ * restores the scalar values of the params struct.  Host pointers, [B]. */
+int mimgpu_set_reg(mimgpu_ctx* ctx, const double* preg, const double* dreg,
+                   void* cuda_stream);
+
+/* Restrict the next direction calls to a subset (the increaseRegularization
+ * retry of src/sqp.cpp:103-116 / src/csqp.cpp:256-269, or the still-active
+ * problems of a batched solve()).  idx == NULL or n < 0 -> all problems. */
+int mimgpu_set_active(mimgpu_ctx* ctx, const int32_t* idx, int32_t n,
+                      void* cuda_stream);
+
+/* Write access to solver members that the reference exposes read-write
+ * (bindings/csqp.cpp:85-98: y, z, rho_vec, dx, du ...).  Host pointer. */
+int mimgpu_set_field(mimgpu_ctx* ctx, int field, const double* src,
+                     void* cuda_stream);
+
+/* ---- the hot path ---------------------------------------------------------- */
+/* SolverSQP::computeDirection (src/sqp.cpp:224-242) without calcDiff:
+ * gap_norm_/merit_, SolverDDP::backwardPass + computeGains (src/ddp.cpp:265-348,
+ * 401-429), SolverSQP::forwardPass (src/sqp.cpp:270-305) and
+ * SolverSQP::checkKKTConditions (src/sqp.cpp:244-268), one fused launch. */
+int mimgpu_sqp_direction(mimgpu_ctx* ctx, const mimgpu_sqp_params* p,
+                         void* cuda_stream);
+
+/* SolverFDDP::computeDirection (src/fddp.cpp:189-204) without calcDiff +
+ * updateExpectedImprovement (src/fddp.cpp:256-279): backward pass, gap_norm_,
+ * dg_, dq_.  Vxx, Vx, K, k, Qu, Quuk stay on the device for download. */
+int mimgpu_fddp_direction(mimgpu_ctx* ctx, const mimgpu_sqp_params* p,
+                          void* cuda_stream);
+
+/* SolverCSQP::calc norms (src/csqp.cpp:417-451, recalc = false):
+ * gap_norm_ = sum_{t=1..T} |fs_t|_1 and constraint_norm_. */
+int mimgpu_csqp_calc_norms(mimgpu_ctx* ctx, void* cuda_stream);
+
+/* SolverCSQP::reset_rho_vec (src/csqp.cpp:534-537): rho_sparse_ = base and
+ * apply_rho_update (src/csqp.cpp:539-582).  solve() calls it at iter_ == 0
+ * (src/csqp.cpp:231-234,248-250). */
+int mimgpu_csqp_reset_rho(mimgpu_ctx* ctx, const mimgpu_csqp_params* p,
+                          void* cuda_stream);
+
+/* SolverCSQP::computeDirection (src/csqp.cpp:454-517) with everything it
+ * drives: reset_params (:170-193), backwardPass_without_constraints /
+ * forwardPass_without_constraints (:804-898, :649-669), backwardPass (:671-802),
+ * backwardPass_without_rho_update (:1025-1108), forwardPass (:630-647),
+ * update_lagrangian_parameters (:1196-1340), update_rho_vec /
+ * apply_rho_update (:519-582); followed, when with_kkt != 0, by
+ * SolverCSQP::checkKKTConditions (:584-628).  The whole ADMM loop runs on the
+ * device; qp_iters[b] follows the reference's for-loop semantics
+ * (max_qp_iters+1 on exhaustion). */
+int mimgpu_csqp_direction(mimgpu_ctx* ctx, const mimgpu_csqp_params* p,
+                          int with_kkt, void* cuda_stream);
+
+/* ---- data out -------------------------------------------------------------- */
+/* Copies one solver member of all B problems to host memory `dst`
+ * (async on `stream`; synchronise the stream before reading). */
+int mimgpu_download(mimgpu_ctx* ctx, int field, double* dst, void* cuda_stream);
+/* Device pointer of a field (for callers that keep results on the GPU). */
+int mimgpu_field_ptr(mimgpu_ctx* ctx, int field, double** dev_ptr,
+                     int64_t* n_doubles);
+/* Per-problem scalars: dst [B] doubles. */
+int mimgpu_scalar(mimgpu_ctx* ctx, int which, double* dst, void* cuda_stream);
+/* qp_iters[B] (CSQP; 0 for SQP) and status[B]; either may be NULL. */
+int mimgpu_iters_status(mimgpu_ctx* ctx, int32_t* qp_iters, int32_t* status,
+                        void* cuda_stream);
+/* Batch-wide reduction on the device, result copied to host (synchronises
+ * `stream`).  With several GPUs the caller all-reduces these five numbers. */
+int mimgpu_summary_reduce(mimgpu_ctx* ctx, double termination_tol,
+                          mimgpu_summary* out, void* cuda_stream);
+/* Number of kernel launches this ctx has enqueued since creation. */
+int64_t mimgpu_launch_count(const mimgpu_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MIMGPU_H_ */

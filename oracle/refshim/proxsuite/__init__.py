@@ -1,0 +1,1 @@
+"""Empty stand-in (import-only); see oracle/refshim/README.md."""
