@@ -259,10 +259,19 @@ int mimgpu_scalar(mimgpu_ctx* ctx, int which, double* dst, void* cuda_stream);
 /* qp_iters[B] (CSQP; 0 for SQP) and status[B]; either may be NULL. */
 int mimgpu_iters_status(mimgpu_ctx* ctx, int32_t* qp_iters, int32_t* status,
                         void* cuda_stream);
+/* converged[B] (CSQP): 1 when the ADMM loop broke on the tolerance test
+ * (src/csqp.cpp:508-511), 0 when max_qp_iters was exhausted. */
+int mimgpu_converged(mimgpu_ctx* ctx, int32_t* converged, void* cuda_stream);
 /* Batch-wide reduction on the device, result copied to host (synchronises
  * `stream`).  With several GPUs the caller all-reduces these five numbers. */
 int mimgpu_summary_reduce(mimgpu_ctx* ctx, double termination_tol,
                           mimgpu_summary* out, void* cuda_stream);
+/* cudaStreamSynchronize(stream) on the ctx's device. */
+int mimgpu_stream_sync(mimgpu_ctx* ctx, void* cuda_stream);
+/* Roofline denominators that MEASURED_PEAKS.json does not carry: FP64 FMA (DFMA,
+ * CUDA cores) and FP64 tensor (DMMA m8n8k4) throughput in TFLOP/s, and streaming-read
+ * HBM bandwidth in GB/s, measured on `device` with register-resident loops. */
+int mimgpu_measure_peaks(int device, double* dfma_tflops, double* dmma_tflops, double* hbm_read_gbs);
 /* Number of kernel launches this ctx has enqueued since creation. */
 int64_t mimgpu_launch_count(const mimgpu_ctx* ctx);
 

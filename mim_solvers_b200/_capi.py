@@ -108,7 +108,7 @@ SYMBOLS = (
     "mimgpu_set_active", "mimgpu_set_field", "mimgpu_sqp_direction",
     "mimgpu_fddp_direction", "mimgpu_csqp_calc_norms", "mimgpu_csqp_reset_rho",
     "mimgpu_csqp_direction", "mimgpu_download", "mimgpu_field_ptr", "mimgpu_scalar",
-    "mimgpu_iters_status", "mimgpu_summary_reduce", "mimgpu_launch_count",
+    "mimgpu_iters_status", "mimgpu_converged", "mimgpu_summary_reduce", "mimgpu_launch_count", "mimgpu_stream_sync", "mimgpu_measure_peaks",
 )
 
 _lib = None
@@ -136,7 +136,10 @@ def _declare(lib):
     lib.mimgpu_field_ptr.argtypes = [vp, C.c_int, C.POINTER(vp), C.POINTER(i64)]
     lib.mimgpu_scalar.argtypes = [vp, C.c_int, vp, vp]
     lib.mimgpu_iters_status.argtypes = [vp, vp, vp, vp]
+    lib.mimgpu_converged.argtypes = [vp, vp, vp]
     lib.mimgpu_summary_reduce.argtypes = [vp, C.c_double, C.POINTER(Summary), vp]
+    lib.mimgpu_stream_sync.argtypes = [vp, vp]
+    lib.mimgpu_measure_peaks.argtypes = [C.c_int, c_double_p, c_double_p, c_double_p]
     lib.mimgpu_launch_count.argtypes = [vp]
     lib.mimgpu_launch_count.restype = i64
     for name in SYMBOLS:

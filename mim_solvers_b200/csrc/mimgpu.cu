@@ -1,0 +1,533 @@
+/*
+ * mimgpu.cu -- C ABI (include/mimgpu.h) of the B200-native batched OCP-QP engine.
+ *
+ * Thin host layer: owns the device buffers of one shape bucket, copies the
+ * derivative tensors in, launches the direction kernels on the caller's stream and
+ * copies solver members out.  No CPU fallback: without a CUDA device every entry
+ * point returns MIMGPU_ERR_NODEVICE / MIMGPU_ERR_CUDA.
+ */
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "kernels_generic.cuh"
+#include "kernels_small.cuh"
+
+using namespace mimgpu;
+
+/* ------------------------------------------------------------------ errors */
+static thread_local std::string g_err;
+static int fail(int code, const std::string& msg) {
+  g_err = msg;
+  return code;
+}
+#define CU(call)                                                                                   \
+  do {                                                                                             \
+    cudaError_t e_ = (call);                                                                       \
+    if (e_ != cudaSuccess)                                                                         \
+      return fail(MIMGPU_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));            \
+  } while (0)
+
+/* --------------------------------------------------------------------- ctx */
+struct mimgpu_ctx {
+  int device = 0;
+  mimgpu_shape sh{};
+  KArgs k{};                       /* device pointers handed to the kernels */
+  double* in_buf = nullptr;        /* owned copy of the derivatives (MEM_HOST uploads) */
+  size_t in_doubles = 0;
+  bool have_inputs = false;
+  double* state_buf = nullptr;     /* all solver members, one allocation */
+  size_t state_doubles = 0;
+  double* field[MIMGPU_F_COUNT] = {};
+  size_t field_n[MIMGPU_F_COUNT] = {};
+  int32_t* ibuf = nullptr;         /* qp_iters, status, converged, active */
+  double* reg_buf = nullptr;       /* preg[B], dreg[B] */
+  void* summary_dev = nullptr;
+  int64_t launches = 0;
+  int nt = 32;                     /* CTA size of the generic kernels */
+  int smem_bytes = 0;
+  int sm_count = 148;
+  int use_small = 0;               /* specialised small-shape kernel available */
+};
+
+static size_t deriv_sizes(const mimgpu_shape& s, size_t n[20]) {
+  const size_t B = s.B, T = s.T, nx = s.nx, nu = s.nu, ng = s.ng, ngT = s.ngT;
+  size_t i = 0, tot = 0;
+  n[i++] = B * T * nx * nx;  /* Fx */
+  n[i++] = B * T * nx * nu;  /* Fu */
+  n[i++] = B * T * nx * nx;  /* Lxx */
+  n[i++] = B * T * nx * nu;  /* Lxu */
+  n[i++] = B * T * nu * nu;  /* Luu */
+  n[i++] = B * T * nx;       /* Lx */
+  n[i++] = B * T * nu;       /* Lu */
+  n[i++] = B * (T + 1) * nx; /* fs */
+  n[i++] = B * nx * nx;      /* LxxT */
+  n[i++] = B * nx;           /* LxT */
+  n[i++] = B * T * ng * nx;  /* Gx */
+  n[i++] = B * T * ng * nu;  /* Gu */
+  n[i++] = B * T * ng;       /* g */
+  n[i++] = B * T * ng;       /* g_lb */
+  n[i++] = B * T * ng;       /* g_ub */
+  n[i++] = B * ngT * nx;     /* GxT */
+  n[i++] = B * ngT;          /* gT */
+  n[i++] = B * ngT;          /* g_lbT */
+  n[i++] = B * ngT;          /* g_ubT */
+  n[i++] = B;                /* cost */
+  for (size_t j = 0; j < 20; ++j) tot += (n[j] + 1) & ~(size_t)1;
+  return tot;
+}
+
+static const double** deriv_slots(KArgs& k, const double** out[20]) {
+  const double** p[20] = {&k.Fx, &k.Fu, &k.Lxx, &k.Lxu, &k.Luu, &k.Lx, &k.Lu, &k.fs, &k.LxxT, &k.LxT,
+                          &k.Gx, &k.Gu, &k.g, &k.glb, &k.gub, &k.GxT, &k.gT, &k.glbT, &k.gubT, &k.cost};
+  for (int i = 0; i < 20; ++i) out[i] = p[i];
+  return nullptr;
+}
+
+static void field_sizes(const mimgpu_shape& s, size_t n[MIMGPU_F_COUNT]) {
+  const size_t B = s.B, T = s.T, nx = s.nx, nu = s.nu, nc = T * s.ng + s.ngT;
+  n[MIMGPU_F_DX] = B * (T + 1) * nx;
+  n[MIMGPU_F_DU] = B * T * nu;
+  n[MIMGPU_F_LAG_MUL] = B * (T + 1) * nx;
+  n[MIMGPU_F_DX_TILDE] = B * (T + 1) * nx;
+  n[MIMGPU_F_DU_TILDE] = B * T * nu;
+  n[MIMGPU_F_Y] = B * nc;
+  n[MIMGPU_F_Z] = B * nc;
+  n[MIMGPU_F_RHO_VEC] = B * nc;
+  n[MIMGPU_F_VXX] = B * (T + 1) * nx * nx;
+  n[MIMGPU_F_VX] = B * (T + 1) * nx;
+  n[MIMGPU_F_K] = B * T * nu * nx;
+  n[MIMGPU_F_KFF] = B * T * nu;
+  n[MIMGPU_F_QU] = B * T * nu;
+  n[MIMGPU_F_QUUK] = B * T * nu;
+  n[MIMGPU_F_QUU_LLT] = B * T * nu * nu;
+}
+
+/* ------------------------------------------------------------------ kernels */
+__global__ void __launch_bounds__(512) k_sqp_direction_generic(KArgs a, SqpKPar kp) {
+  extern __shared__ double sm[];
+  if ((int)blockIdx.x >= a.n_active) return;
+  const int b = a.active ? a.active[blockIdx.x] : (int)blockIdx.x;
+  sqp_direction_body(a, b, sm, kp);
+}
+__global__ void __launch_bounds__(512) k_fddp_direction_generic(KArgs a, SqpKPar kp) {
+  extern __shared__ double sm[];
+  if ((int)blockIdx.x >= a.n_active) return;
+  const int b = a.active ? a.active[blockIdx.x] : (int)blockIdx.x;
+  fddp_direction_body(a, b, sm, kp);
+}
+__global__ void __launch_bounds__(512) k_csqp_direction_generic(KArgs a, CsqpKPar kp) {
+  extern __shared__ double sm[];
+  if ((int)blockIdx.x >= a.n_active) return;
+  const int b = a.active ? a.active[blockIdx.x] : (int)blockIdx.x;
+  csqp_direction_body(a, b, sm, kp);
+}
+__global__ void k_csqp_reset_rho(KArgs a, double base, double rho_min) {
+  if ((int)blockIdx.x >= a.n_active) return;
+  const int b = a.active ? a.active[blockIdx.x] : (int)blockIdx.x;
+  csqp_reset_rho_body(a, b, base, rho_min);
+}
+__global__ void k_csqp_calc_norms(KArgs a) {
+  __shared__ double red[64];
+  if ((int)blockIdx.x >= a.n_active) return;
+  const int b = a.active ? a.active[blockIdx.x] : (int)blockIdx.x;
+  csqp_calc_norms_body(a, b, red);
+}
+__global__ void k_fill(double* p, size_t n, double v) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) p[i] = v;
+}
+struct SummaryDev {
+  double max_kkt;
+  long long sum_it, max_it, n_conv, n_fail;
+};
+__global__ void k_summary(const double* kkt, const int32_t* it, const int32_t* st, const int32_t* conv, int B,
+                          double tol, int csqp, SummaryDev* out) {
+  __shared__ double smax[32];
+  __shared__ long long ssum[32], smx[32], scv[32], sfl[32];
+  double m = 0.0;
+  long long s = 0, mx = 0, cv = 0, fl = 0;
+  for (int b = threadIdx.x; b < B; b += blockDim.x) {
+    m = nmax(m, kkt[b]);
+    s += it[b];
+    mx = it[b] > mx ? it[b] : mx;
+    cv += csqp ? (conv[b] != 0) : (kkt[b] <= tol);
+    fl += (st[b] != 0);
+  }
+  for (int o = 16; o; o >>= 1) {
+    m = nmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+    s += __shfl_xor_sync(0xffffffffu, s, o);
+    long long t = __shfl_xor_sync(0xffffffffu, mx, o);
+    mx = t > mx ? t : mx;
+    cv += __shfl_xor_sync(0xffffffffu, cv, o);
+    fl += __shfl_xor_sync(0xffffffffu, fl, o);
+  }
+  const int w = threadIdx.x >> 5;
+  if ((threadIdx.x & 31) == 0) { smax[w] = m; ssum[w] = s; smx[w] = mx; scv[w] = cv; sfl[w] = fl; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const int nw = blockDim.x >> 5;
+    for (int i = 1; i < nw; ++i) {
+      m = nmax(m, smax[i]); s += ssum[i]; mx = smx[i] > mx ? smx[i] : mx; cv += scv[i]; fl += sfl[i];
+    }
+    out->max_kkt = m; out->sum_it = s; out->max_it = mx; out->n_conv = cv; out->n_fail = fl;
+  }
+}
+
+/* ---------------------------------------------------------------- lifecycle */
+extern "C" {
+
+int mimgpu_abi_version(void) { return MIMGPU_ABI_VERSION; }
+
+const char* mimgpu_last_error(void) { return g_err.c_str(); }
+
+int mimgpu_device_count(int* n) {
+  if (!n) return fail(MIMGPU_ERR_INVALID, "null pointer");
+  int c = 0;
+  cudaError_t e = cudaGetDeviceCount(&c);
+  if (e != cudaSuccess) {
+    *n = 0;
+    cudaGetLastError();
+    return fail(MIMGPU_ERR_NODEVICE, std::string("cudaGetDeviceCount: ") + cudaGetErrorString(e));
+  }
+  *n = c;
+  return MIMGPU_OK;
+}
+
+static int configure_launch(mimgpu_ctx* c) {
+  const mimgpu_shape& s = c->sh;
+  cudaDeviceProp prop;
+  CU(cudaGetDeviceProperties(&prop, c->device));
+  c->sm_count = prop.multiProcessorCount;
+  const int max_smem = (int)prop.sharedMemPerBlockOptin;
+  int stage = 1;
+  Smem L = smem_layout(s.nx, s.nu, s.ng, s.ngT, stage);
+  if (L.total * 8 > max_smem) {
+    stage = 0;
+    L = smem_layout(s.nx, s.nu, s.ng, s.ngT, stage);
+  }
+  if (L.total * 8 > max_smem)
+    return fail(MIMGPU_ERR_UNSUPPORTED, "shape needs " + std::to_string(L.total * 8) + " B of shared memory per CTA");
+  c->k.stage_fx = stage;
+  c->smem_bytes = L.total * 8;
+  int nt = ((s.nx * s.nx / 8 + 31) / 32) * 32;
+  if (nt < 32) nt = 32;
+  if (nt > 512) nt = 512;
+  c->nt = nt;
+  CU(cudaFuncSetAttribute(k_sqp_direction_generic, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+  CU(cudaFuncSetAttribute(k_fddp_direction_generic, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+  CU(cudaFuncSetAttribute(k_csqp_direction_generic, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+  c->use_small = small_kernels_configure(s);
+  return MIMGPU_OK;
+}
+
+int mimgpu_create(mimgpu_ctx** out, int device, const mimgpu_shape* shape) {
+  if (!out || !shape) return fail(MIMGPU_ERR_INVALID, "null pointer");
+  *out = nullptr;
+  const mimgpu_shape& s = *shape;
+  if (s.B < 1 || s.T < 1 || s.nx < 1 || s.nu < 0 || s.ng < 0 || s.ngT < 0)
+    return fail(MIMGPU_ERR_INVALID, "bad shape");
+  int ndev = 0;
+  int rc = mimgpu_device_count(&ndev);
+  if (rc != MIMGPU_OK) return rc;
+  if (ndev == 0) return fail(MIMGPU_ERR_NODEVICE, "no CUDA device: there is no CPU fallback");
+  if (device < 0 || device >= ndev) return fail(MIMGPU_ERR_INVALID, "bad device index");
+  CU(cudaSetDevice(device));
+  mimgpu_ctx* c = new (std::nothrow) mimgpu_ctx();
+  if (!c) return fail(MIMGPU_ERR_INVALID, "out of host memory");
+  c->device = device;
+  c->sh = s;
+  c->k.sh = s;
+  rc = configure_launch(c);
+  if (rc != MIMGPU_OK) { delete c; return rc; }
+  /* solver members: zero-initialised as in src/ddp.cpp:447-502, src/csqp.cpp:24-168 */
+  field_sizes(s, c->field_n);
+  size_t tot = 0;
+  for (int f = 0; f < MIMGPU_F_COUNT; ++f) tot += (c->field_n[f] + 1) & ~(size_t)1;
+  const size_t n_vfs = ((size_t)s.B * s.T * s.nx + 1) & ~(size_t)1;
+  const size_t n_scal = ((size_t)MIMGPU_S_COUNT * s.B + 1) & ~(size_t)1;
+  tot += n_vfs + n_scal;
+  c->state_doubles = tot;
+  cudaError_t e = cudaMalloc(&c->state_buf, tot * sizeof(double));
+  if (e != cudaSuccess) { delete c; return fail(MIMGPU_ERR_CUDA, std::string("cudaMalloc(state): ") + cudaGetErrorString(e)); }
+  cudaMemset(c->state_buf, 0, tot * sizeof(double));
+  double* p = c->state_buf;
+  for (int f = 0; f < MIMGPU_F_COUNT; ++f) { c->field[f] = p; p += (c->field_n[f] + 1) & ~(size_t)1; }
+  c->k.Vxx_fs = p; p += n_vfs;
+  c->k.scal = p;
+  c->k.dx = c->field[MIMGPU_F_DX]; c->k.du = c->field[MIMGPU_F_DU]; c->k.lag = c->field[MIMGPU_F_LAG_MUL];
+  c->k.dxt = c->field[MIMGPU_F_DX_TILDE]; c->k.dut = c->field[MIMGPU_F_DU_TILDE];
+  c->k.y = c->field[MIMGPU_F_Y]; c->k.z = c->field[MIMGPU_F_Z]; c->k.rho = c->field[MIMGPU_F_RHO_VEC];
+  c->k.Vxx = c->field[MIMGPU_F_VXX]; c->k.Vx = c->field[MIMGPU_F_VX]; c->k.K = c->field[MIMGPU_F_K];
+  c->k.kff = c->field[MIMGPU_F_KFF]; c->k.Qu = c->field[MIMGPU_F_QU]; c->k.Quuk = c->field[MIMGPU_F_QUUK];
+  c->k.L = c->field[MIMGPU_F_QUU_LLT];
+  /* KKT_ = +inf (include/mim_solvers/sqp.hpp:182-183), rho_sparse_ = 1e-1 (csqp.hpp:323) */
+  k_fill<<<(s.B + 255) / 256, 256>>>(c->k.scal + (size_t)MIMGPU_S_KKT * s.B, s.B, INFINITY);
+  k_fill<<<(s.B + 255) / 256, 256>>>(c->k.scal + (size_t)MIMGPU_S_RHO_SPARSE * s.B, s.B, 1e-1);
+  e = cudaMalloc(&c->ibuf, sizeof(int32_t) * 4 * (size_t)s.B);
+  if (e == cudaSuccess) e = cudaMemset(c->ibuf, 0, sizeof(int32_t) * 4 * (size_t)s.B);
+  if (e == cudaSuccess) e = cudaMalloc(&c->reg_buf, sizeof(double) * 2 * (size_t)s.B);
+  if (e == cudaSuccess) e = cudaMalloc(&c->summary_dev, sizeof(SummaryDev));
+  if (e == cudaSuccess) e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) {
+    mimgpu_destroy(c);
+    return fail(MIMGPU_ERR_CUDA, std::string("cudaMalloc(aux): ") + cudaGetErrorString(e));
+  }
+  c->k.qp_iters = c->ibuf; c->k.status = c->ibuf + s.B; c->k.converged = c->ibuf + 2 * (size_t)s.B;
+  c->k.active = nullptr; c->k.n_active = s.B;
+  c->k.preg_arr = nullptr; c->k.dreg_arr = nullptr;
+  *out = c;
+  return MIMGPU_OK;
+}
+
+void mimgpu_destroy(mimgpu_ctx* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  cudaFree(c->in_buf); cudaFree(c->state_buf); cudaFree(c->ibuf); cudaFree(c->reg_buf); cudaFree(c->summary_dev);
+  delete c;
+}
+
+int mimgpu_get_shape(const mimgpu_ctx* c, mimgpu_shape* shape) {
+  if (!c || !shape) return fail(MIMGPU_ERR_INVALID, "null pointer");
+  *shape = c->sh;
+  return MIMGPU_OK;
+}
+
+/* ------------------------------------------------------------------ data in */
+int mimgpu_upload(mimgpu_ctx* c, const mimgpu_derivs* d, int memkind, void* stream) {
+  if (!c || !d) return fail(MIMGPU_ERR_INVALID, "null pointer");
+  cudaStream_t st = (cudaStream_t)stream;
+  CU(cudaSetDevice(c->device));
+  size_t n[20];
+  const size_t tot = deriv_sizes(c->sh, n);
+  const double* src[20] = {d->Fx, d->Fu, d->Lxx, d->Lxu, d->Luu, d->Lx, d->Lu, d->fs, d->LxxT, d->LxT,
+                           d->Gx, d->Gu, d->g, d->g_lb, d->g_ub, d->GxT, d->gT, d->g_lbT, d->g_ubT, d->cost};
+  for (int i = 0; i < 19; ++i)
+    if (n[i] && !src[i]) return fail(MIMGPU_ERR_INVALID, "missing derivative array #" + std::to_string(i));
+  const double** slot[20];
+  deriv_slots(c->k, slot);
+  if (memkind == MIMGPU_MEM_DEVICE) {
+    for (int i = 0; i < 20; ++i) *slot[i] = n[i] ? src[i] : nullptr;
+    c->have_inputs = true;
+    return MIMGPU_OK;
+  }
+  if (memkind != MIMGPU_MEM_HOST) return fail(MIMGPU_ERR_INVALID, "bad memkind");
+  if (!c->in_buf) {
+    CU(cudaMalloc(&c->in_buf, tot * sizeof(double)));
+    c->in_doubles = tot;
+  }
+  double* p = c->in_buf;
+  for (int i = 0; i < 20; ++i) {
+    if (n[i] && src[i]) {
+      CU(cudaMemcpyAsync(p, src[i], n[i] * sizeof(double), cudaMemcpyHostToDevice, st));
+      *slot[i] = p;
+    } else {
+      *slot[i] = nullptr;
+    }
+    p += (n[i] + 1) & ~(size_t)1;
+  }
+  c->have_inputs = true;
+  return MIMGPU_OK;
+}
+
+int mimgpu_set_reg(mimgpu_ctx* c, const double* preg, const double* dreg, void* stream) {
+  if (!c) return fail(MIMGPU_ERR_INVALID, "null pointer");
+  cudaStream_t st = (cudaStream_t)stream;
+  CU(cudaSetDevice(c->device));
+  const size_t B = c->sh.B;
+  if (preg) {
+    CU(cudaMemcpyAsync(c->reg_buf, preg, B * sizeof(double), cudaMemcpyHostToDevice, st));
+    c->k.preg_arr = c->reg_buf;
+  } else {
+    c->k.preg_arr = nullptr;
+  }
+  if (dreg) {
+    CU(cudaMemcpyAsync(c->reg_buf + B, dreg, B * sizeof(double), cudaMemcpyHostToDevice, st));
+    c->k.dreg_arr = c->reg_buf + B;
+  } else {
+    c->k.dreg_arr = nullptr;
+  }
+  return MIMGPU_OK;
+}
+
+int mimgpu_set_active(mimgpu_ctx* c, const int32_t* idx, int32_t n, void* stream) {
+  if (!c) return fail(MIMGPU_ERR_INVALID, "null pointer");
+  cudaStream_t st = (cudaStream_t)stream;
+  CU(cudaSetDevice(c->device));
+  if (!idx || n < 0) {
+    c->k.active = nullptr;
+    c->k.n_active = c->sh.B;
+    return MIMGPU_OK;
+  }
+  if (n > c->sh.B) return fail(MIMGPU_ERR_INVALID, "more active problems than B");
+  for (int i = 0; i < n; ++i)
+    if (idx[i] < 0 || idx[i] >= c->sh.B) return fail(MIMGPU_ERR_INVALID, "active index out of range");
+  int32_t* dst = c->ibuf + 3 * (size_t)c->sh.B;
+  if (n) CU(cudaMemcpyAsync(dst, idx, n * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+  c->k.active = dst;
+  c->k.n_active = n;
+  return MIMGPU_OK;
+}
+
+int mimgpu_set_field(mimgpu_ctx* c, int field, const double* src, void* stream) {
+  if (!c || !src) return fail(MIMGPU_ERR_INVALID, "null pointer");
+  if (field < 0 || field >= MIMGPU_F_COUNT) return fail(MIMGPU_ERR_INVALID, "bad field id");
+  CU(cudaSetDevice(c->device));
+  if (c->field_n[field])
+    CU(cudaMemcpyAsync(c->field[field], src, c->field_n[field] * sizeof(double), cudaMemcpyHostToDevice,
+                       (cudaStream_t)stream));
+  return MIMGPU_OK;
+}
+
+/* ------------------------------------------------------------- the hot path */
+static int pre_launch(mimgpu_ctx* c) {
+  if (!c) return fail(MIMGPU_ERR_INVALID, "null ctx");
+  if (!c->have_inputs) return fail(MIMGPU_ERR_STATE, "direction requested before mimgpu_upload");
+  cudaError_t e = cudaSetDevice(c->device);
+  if (e != cudaSuccess) return fail(MIMGPU_ERR_CUDA, cudaGetErrorString(e));
+  return MIMGPU_OK;
+}
+static int post_launch(mimgpu_ctx* c, const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(MIMGPU_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+  c->launches++;
+  return MIMGPU_OK;
+}
+
+int mimgpu_sqp_direction(mimgpu_ctx* c, const mimgpu_sqp_params* p, void* stream) {
+  int rc = pre_launch(c);
+  if (rc) return rc;
+  if (!p) return fail(MIMGPU_ERR_INVALID, "null params");
+  if (c->k.n_active == 0) return MIMGPU_OK;
+  SqpKPar kp{p->preg, p->dreg, p->mu_dynamic, p->is_feasible};
+  cudaStream_t st = (cudaStream_t)stream;
+  if (c->use_small && getenv("MIMGPU_FORCE_GENERIC") == nullptr) {
+    rc = small_sqp_direction_launch(c->k, kp, c->sm_count, st);
+    if (rc == 0) return post_launch(c, "k_sqp_direction_small");
+    if (rc > 0) return fail(MIMGPU_ERR_CUDA, "small kernel launch configuration failed");
+  }
+  k_sqp_direction_generic<<<c->k.n_active, c->nt, c->smem_bytes, st>>>(c->k, kp);
+  return post_launch(c, "k_sqp_direction_generic");
+}
+
+int mimgpu_fddp_direction(mimgpu_ctx* c, const mimgpu_sqp_params* p, void* stream) {
+  int rc = pre_launch(c);
+  if (rc) return rc;
+  if (!p) return fail(MIMGPU_ERR_INVALID, "null params");
+  if (c->k.n_active == 0) return MIMGPU_OK;
+  SqpKPar kp{p->preg, p->dreg, p->mu_dynamic, p->is_feasible};
+  k_fddp_direction_generic<<<c->k.n_active, c->nt, c->smem_bytes, (cudaStream_t)stream>>>(c->k, kp);
+  return post_launch(c, "k_fddp_direction_generic");
+}
+
+int mimgpu_csqp_calc_norms(mimgpu_ctx* c, void* stream) {
+  int rc = pre_launch(c);
+  if (rc) return rc;
+  if (c->k.n_active == 0) return MIMGPU_OK;
+  k_csqp_calc_norms<<<c->k.n_active, 128, 0, (cudaStream_t)stream>>>(c->k);
+  return post_launch(c, "k_csqp_calc_norms");
+}
+
+int mimgpu_csqp_reset_rho(mimgpu_ctx* c, const mimgpu_csqp_params* p, void* stream) {
+  int rc = pre_launch(c);
+  if (rc) return rc;
+  if (!p) return fail(MIMGPU_ERR_INVALID, "null params");
+  if (c->k.n_active == 0) return MIMGPU_OK;
+  k_csqp_reset_rho<<<c->k.n_active, 128, 0, (cudaStream_t)stream>>>(c->k, p->rho_sparse_base, p->rho_min);
+  return post_launch(c, "k_csqp_reset_rho");
+}
+
+int mimgpu_csqp_direction(mimgpu_ctx* c, const mimgpu_csqp_params* p, int with_kkt, void* stream) {
+  int rc = pre_launch(c);
+  if (rc) return rc;
+  if (!p) return fail(MIMGPU_ERR_INVALID, "null params");
+  if (p->rho_update_interval < 1 || p->max_qp_iters < 0) return fail(MIMGPU_ERR_INVALID, "bad CSQP parameters");
+  if (c->k.n_active == 0) return MIMGPU_OK;
+  CsqpKPar kp;
+  kp.q = *p;
+  kp.with_kkt = with_kkt;
+  k_csqp_direction_generic<<<c->k.n_active, c->nt, c->smem_bytes, (cudaStream_t)stream>>>(c->k, kp);
+  return post_launch(c, "k_csqp_direction_generic");
+}
+
+/* ----------------------------------------------------------------- data out */
+int mimgpu_download(mimgpu_ctx* c, int field, double* dst, void* stream) {
+  if (!c || !dst) return fail(MIMGPU_ERR_INVALID, "null pointer");
+  if (field < 0 || field >= MIMGPU_F_COUNT) return fail(MIMGPU_ERR_INVALID, "bad field id");
+  CU(cudaSetDevice(c->device));
+  if (c->field_n[field])
+    CU(cudaMemcpyAsync(dst, c->field[field], c->field_n[field] * sizeof(double), cudaMemcpyDeviceToHost,
+                       (cudaStream_t)stream));
+  return MIMGPU_OK;
+}
+
+int mimgpu_field_ptr(mimgpu_ctx* c, int field, double** dev_ptr, int64_t* n_doubles) {
+  if (!c) return fail(MIMGPU_ERR_INVALID, "null pointer");
+  if (field < 0 || field >= MIMGPU_F_COUNT) return fail(MIMGPU_ERR_INVALID, "bad field id");
+  if (dev_ptr) *dev_ptr = c->field[field];
+  if (n_doubles) *n_doubles = (int64_t)c->field_n[field];
+  return MIMGPU_OK;
+}
+
+int mimgpu_scalar(mimgpu_ctx* c, int which, double* dst, void* stream) {
+  if (!c || !dst) return fail(MIMGPU_ERR_INVALID, "null pointer");
+  if (which < 0 || which >= MIMGPU_S_COUNT) return fail(MIMGPU_ERR_INVALID, "bad scalar id");
+  CU(cudaSetDevice(c->device));
+  CU(cudaMemcpyAsync(dst, c->k.scal + (size_t)which * c->sh.B, c->sh.B * sizeof(double), cudaMemcpyDeviceToHost,
+                     (cudaStream_t)stream));
+  return MIMGPU_OK;
+}
+
+int mimgpu_iters_status(mimgpu_ctx* c, int32_t* qp_iters, int32_t* status, void* stream) {
+  if (!c) return fail(MIMGPU_ERR_INVALID, "null pointer");
+  CU(cudaSetDevice(c->device));
+  const size_t B = c->sh.B;
+  if (qp_iters)
+    CU(cudaMemcpyAsync(qp_iters, c->k.qp_iters, B * sizeof(int32_t), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  if (status)
+    CU(cudaMemcpyAsync(status, c->k.status, B * sizeof(int32_t), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  return MIMGPU_OK;
+}
+
+int mimgpu_converged(mimgpu_ctx* c, int32_t* converged, void* stream) {
+  if (!c || !converged) return fail(MIMGPU_ERR_INVALID, "null pointer");
+  CU(cudaSetDevice(c->device));
+  CU(cudaMemcpyAsync(converged, c->k.converged, c->sh.B * sizeof(int32_t), cudaMemcpyDeviceToHost,
+                     (cudaStream_t)stream));
+  return MIMGPU_OK;
+}
+
+int mimgpu_summary_reduce(mimgpu_ctx* c, double termination_tol, mimgpu_summary* out, void* stream) {
+  if (!c || !out) return fail(MIMGPU_ERR_INVALID, "null pointer");
+  CU(cudaSetDevice(c->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  /* csqp = 1 when any ADMM call has set qp_iters (> 0); decided on the device data */
+  int32_t first_it = 0;
+  CU(cudaMemcpyAsync(&first_it, c->k.qp_iters, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  k_summary<<<1, 1024, 0, st>>>(c->k.scal + (size_t)MIMGPU_S_KKT * c->sh.B, c->k.qp_iters, c->k.status,
+                                c->k.converged, c->sh.B, termination_tol, first_it > 0, (SummaryDev*)c->summary_dev);
+  int rc = post_launch(c, "k_summary");
+  if (rc) return rc;
+  SummaryDev h;
+  CU(cudaMemcpyAsync(&h, c->summary_dev, sizeof(h), cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  out->max_kkt = h.max_kkt; out->sum_qp_iters = h.sum_it; out->max_qp_iters = h.max_it;
+  out->n_converged = h.n_conv; out->n_failed = h.n_fail;
+  return MIMGPU_OK;
+}
+
+int mimgpu_stream_sync(mimgpu_ctx* c, void* stream) {
+  if (!c) return fail(MIMGPU_ERR_INVALID, "null pointer");
+  CU(cudaSetDevice(c->device));
+  CU(cudaStreamSynchronize((cudaStream_t)stream));
+  return MIMGPU_OK;
+}
+
+int64_t mimgpu_launch_count(const mimgpu_ctx* c) { return c ? c->launches : 0; }
+
+} /* extern "C" */

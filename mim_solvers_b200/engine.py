@@ -1,0 +1,170 @@
+"""BatchEngine: Python handle of one `mimgpu_ctx` (include/mimgpu.h) -- the CUDA
+implementation of the computeDirection hot path for a batch of B problems of one shape.
+
+Every compute call goes through the C ABI of libmimgpu.so.  There is NO CPU fallback:
+constructing an engine without the library or without a CUDA device raises MimGpuError.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _capi
+from ._capi import MimGpuError, check
+from .problems import OCPBatch
+
+
+class BatchEngine:
+    """Same method names as the reference solver members they replace
+    (`computeDirection` pieces of SolverSQP / SolverCSQP / SolverFDDP)."""
+
+    def __init__(self, batch: OCPBatch | None = None, *, shape: _capi.Shape | None = None,
+                 device: int = 0, stream: int | None = None):
+        self._lib = _capi.load_library()
+        self._ctx = C.c_void_p()
+        self._shape = batch.shape() if batch is not None else shape
+        if self._shape is None:
+            raise ValueError("need a batch or a shape")
+        self.stream = C.c_void_p(stream) if stream else None
+        self.device = device
+        check(self._lib.mimgpu_create(C.byref(self._ctx), device, C.byref(self._shape)), "mimgpu_create")
+        self._keep = None
+        if batch is not None:
+            self.upload(batch)
+
+    def close(self):
+        if getattr(self, "_ctx", None) and self._ctx.value:
+            self._lib.mimgpu_destroy(self._ctx)
+            self._ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- plumbing ------------------------------------------------------------------
+    @property
+    def shape(self) -> _capi.Shape:
+        return self._shape
+
+    def sync(self):
+        check(self._lib.mimgpu_stream_sync(self._ctx, self.stream), "mimgpu_stream_sync")
+
+    def upload(self, batch: OCPBatch):
+        """Host arrays -> device (async H2D on the engine's stream)."""
+        d = batch.derivs()
+        self._keep = batch
+        check(self._lib.mimgpu_upload(self._ctx, C.byref(d), _capi.MEM_HOST, self.stream), "mimgpu_upload")
+
+    def attach_device(self, tensors: dict):
+        """Device-resident inputs (torch CUDA float64 tensors in the C-ABI layout)."""
+        d = _capi.Derivs()
+        for n in _capi.DERIV_FIELDS:
+            t = tensors.get(n)
+            if t is not None and t.numel():
+                assert t.is_cuda and t.is_contiguous() and str(t.dtype) == "torch.float64", n
+                setattr(d, n, t.data_ptr())
+        self._keep = tensors
+        check(self._lib.mimgpu_upload(self._ctx, C.byref(d), _capi.MEM_DEVICE, self.stream), "mimgpu_upload")
+
+    def set_reg(self, preg=None, dreg=None):
+        p = None if preg is None else np.ascontiguousarray(preg, dtype=np.float64)
+        d = None if dreg is None else np.ascontiguousarray(dreg, dtype=np.float64)
+        check(self._lib.mimgpu_set_reg(self._ctx, _capi.as_ptr(p), _capi.as_ptr(d), self.stream), "mimgpu_set_reg")
+        self.sync()
+
+    def set_active(self, idx=None):
+        if idx is None:
+            check(self._lib.mimgpu_set_active(self._ctx, None, -1, self.stream), "mimgpu_set_active")
+            return
+        a = np.ascontiguousarray(idx, dtype=np.int32)
+        check(self._lib.mimgpu_set_active(self._ctx, a.ctypes.data, len(a), self.stream), "mimgpu_set_active")
+        self.sync()
+
+    def set_field(self, name: str, value):
+        a = np.ascontiguousarray(value, dtype=np.float64).reshape(self._shape.field_shape(name))
+        check(self._lib.mimgpu_set_field(self._ctx, _capi.FIELDS[name], a.ctypes.data, self.stream),
+              "mimgpu_set_field")
+        self.sync()
+
+    # ---- the hot path --------------------------------------------------------------
+    def sqp_direction(self, params=None, with_kkt=True, preg=None, dreg=None):
+        p = params or _capi.default_sqp_params()
+        if preg is not None or dreg is not None:
+            self.set_reg(preg, dreg)
+        check(self._lib.mimgpu_sqp_direction(self._ctx, C.byref(p), self.stream), "mimgpu_sqp_direction")
+
+    def fddp_direction(self, params=None):
+        p = params or _capi.default_sqp_params()
+        check(self._lib.mimgpu_fddp_direction(self._ctx, C.byref(p), self.stream), "mimgpu_fddp_direction")
+
+    def csqp_calc_norms(self):
+        check(self._lib.mimgpu_csqp_calc_norms(self._ctx, self.stream), "mimgpu_csqp_calc_norms")
+
+    def csqp_reset_rho(self, params=None):
+        p = params or _capi.default_csqp_params()
+        check(self._lib.mimgpu_csqp_reset_rho(self._ctx, C.byref(p), self.stream), "mimgpu_csqp_reset_rho")
+
+    def csqp_direction(self, params=None, with_kkt=True):
+        p = params or _capi.default_csqp_params()
+        check(self._lib.mimgpu_csqp_direction(self._ctx, C.byref(p), int(with_kkt), self.stream),
+              "mimgpu_csqp_direction")
+
+    # ---- data out ------------------------------------------------------------------
+    def field(self, name: str) -> np.ndarray:
+        out = np.empty(self._shape.field_shape(name))
+        if out.size:
+            check(self._lib.mimgpu_download(self._ctx, _capi.FIELDS[name], out.ctypes.data, self.stream),
+                  "mimgpu_download")
+            self.sync()
+        return out
+
+    def download_into(self, name: str, out: np.ndarray):
+        """Async D2H into a caller-provided (pinned) array; caller synchronises."""
+        check(self._lib.mimgpu_download(self._ctx, _capi.FIELDS[name], out.ctypes.data, self.stream),
+              "mimgpu_download")
+
+    def scalar(self, name: str) -> np.ndarray:
+        out = np.empty(self._shape.B)
+        check(self._lib.mimgpu_scalar(self._ctx, _capi.SCALARS[name], out.ctypes.data, self.stream), "mimgpu_scalar")
+        self.sync()
+        return out
+
+    def _ints(self):
+        B = self._shape.B
+        it = np.empty(B, dtype=np.int32)
+        st = np.empty(B, dtype=np.int32)
+        cv = np.empty(B, dtype=np.int32)
+        check(self._lib.mimgpu_iters_status(self._ctx, it.ctypes.data, st.ctypes.data, self.stream),
+              "mimgpu_iters_status")
+        check(self._lib.mimgpu_converged(self._ctx, cv.ctypes.data, self.stream), "mimgpu_converged")
+        self.sync()
+        return it, st, cv
+
+    @property
+    def qp_iters(self):
+        return self._ints()[0]
+
+    @property
+    def status(self):
+        return self._ints()[1]
+
+    @property
+    def converged(self):
+        return self._ints()[2]
+
+    def summary(self, termination_tol: float = 1e-6) -> dict:
+        s = _capi.Summary()
+        check(self._lib.mimgpu_summary_reduce(self._ctx, termination_tol, C.byref(s), self.stream),
+              "mimgpu_summary_reduce")
+        return dict(max_kkt=s.max_kkt, sum_qp_iters=s.sum_qp_iters, max_qp_iters=s.max_qp_iters,
+                    n_converged=s.n_converged, n_failed=s.n_failed)
+
+    @property
+    def launch_count(self) -> int:
+        return int(self._lib.mimgpu_launch_count(self._ctx))
+
+
+__all__ = ["BatchEngine", "MimGpuError"]

@@ -1,0 +1,112 @@
+"""GPU parity tests proper: the CUDA path (through the C ABI of libmimgpu.so) against the
+golden vectors (reference NumPy solvers) and against the CPU oracle on seeded batches.
+Bar: 1e-9 relative on dx/du/lag_mul/KKT (1e-8 against the NumPy goldens, see
+golden_checks.py), identical qp_iters."""
+import numpy as np
+import pytest
+
+import golden_checks as gc
+from helpers import golden_names
+from parity_checks import compare_engines_csqp, compare_engines_fddp, compare_engines_sqp
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def eng():
+    from mim_solvers_b200 import _capi
+    from mim_solvers_b200.engine import BatchEngine
+    lib = _capi.load_library()           # raises if the extension is missing: no fallback
+    n = __import__("ctypes").c_int(0)
+    assert lib.mimgpu_device_count(__import__("ctypes").byref(n)) == 0 and n.value > 0, "no CUDA device"
+    return BatchEngine
+
+
+@pytest.mark.parametrize("name", golden_names("sqp_"))
+def test_gpu_sqp_golden(eng, name):
+    gc.check_sqp_golden(lambda b: eng(b), name)
+
+
+@pytest.mark.parametrize("name", golden_names("csqp_"))
+def test_gpu_csqp_golden(eng, name):
+    gc.check_csqp_golden(lambda b: eng(b), name)
+
+
+SQP_SHAPES = [(16, 100, 12, 6), (5, 40, 12, 6), (4, 13, 7, 3), (3, 10, 36, 12), (2, 6, 64, 32),
+              (2, 5, 76, 32), (3, 9, 5, 1), (2, 4, 3, 4)]
+
+
+@pytest.mark.parametrize("B,T,nx,nu", SQP_SHAPES)
+def test_gpu_sqp_vs_oracle(eng, oracle_lib, B, T, nx, nu):
+    from mim_solvers_b200.problems import make_random_batch
+    compare_engines_sqp(lambda b: eng(b), lambda b: oracle_lib.Oracle(b), make_random_batch(B, T, nx, nu))
+
+
+@pytest.mark.parametrize("B,T,nx,nu", [(4, 30, 12, 6), (2, 8, 36, 12)])
+def test_gpu_fddp_vs_oracle(eng, oracle_lib, B, T, nx, nu):
+    from mim_solvers_b200.problems import make_random_batch
+    compare_engines_fddp(lambda b: eng(b), lambda b: oracle_lib.Oracle(b), make_random_batch(B, T, nx, nu))
+
+
+CSQP_SHAPES = [  # B, T, nx, nu, ng, ngT, kwargs
+    (6, 40, 12, 6, 3, 3, dict(box_rows=0)),
+    (4, 20, 12, 6, 0, 0, {}),
+    (3, 12, 36, 12, 16, 0, dict(box_rows=12)),
+    (2, 10, 36, 12, 36, 36, dict(box_rows=36)),
+    (3, 10, 16, 8, 24, 16, dict(eq_frac=0.1)),
+    (2, 5, 64, 32, 96, 64, dict(eq_frac=0.1)),
+    (2, 4, 76, 32, 32, 0, dict(box_rows=32)),
+]
+
+
+@pytest.mark.parametrize("B,T,nx,nu,ng,ngT,kw", CSQP_SHAPES)
+def test_gpu_csqp_vs_oracle(eng, oracle_lib, B, T, nx, nu, ng, ngT, kw):
+    from mim_solvers_b200 import _capi
+    from mim_solvers_b200.problems import make_random_batch
+    batch = make_random_batch(B, T, nx, nu, ng=ng, ngT=ngT, **kw)
+    p = _capi.default_csqp_params(max_qp_iters=200)
+    compare_engines_csqp(lambda b: eng(b), lambda b: oracle_lib.Oracle(b), batch, params=p, n_calls=2)
+
+
+def test_gpu_csqp_benchmark_protocol(eng, oracle_lib):
+    """benchmarks/solo12.cpp:213-216: eps_abs = eps_rel = 0, 50 iterations, no eq. guess."""
+    from mim_solvers_b200 import _capi
+    from mim_solvers_b200.problems import make_random_batch
+    batch = make_random_batch(4, 15, 12, 6, ng=6, ngT=6)
+    p = _capi.default_csqp_params(max_qp_iters=50, eps_abs=0.0, eps_rel=0.0, equality_qp_initial_guess=0)
+    g, o = compare_engines_csqp(lambda b: eng(b), lambda b: oracle_lib.Oracle(b), batch, params=p, n_calls=1)
+    assert np.all(g.qp_iters == 51)
+
+
+def test_gpu_llt_failure_status(eng, oracle_lib):
+    """Fault injection: indefinite Luu -> status LLT at the failing knot (src/ddp.cpp:415-419)."""
+    from mim_solvers_b200 import _capi
+    from mim_solvers_b200.problems import make_random_batch
+    batch = make_random_batch(4, 8, 6, 3)
+    batch.mat("Luu")[1, 5] = -10.0 * np.eye(3)
+    g, o = eng(batch), oracle_lib.Oracle(batch)
+    g.sqp_direction(); o.sqp_direction()
+    assert np.array_equal(g.status, np.asarray(o.status))
+    assert g.status[1] == (_capi.STATUS_LLT | (5 << 8)) and g.status[0] == 0
+    # retry only the failed problem with a larger regularisation (src/sqp.cpp:103-116)
+    g.set_active([1])
+    preg = np.full(4, 1e-9); preg[1] = 20.0
+    g.sqp_direction(preg=preg, dreg=preg)
+    o.sqp_direction(preg=preg, dreg=preg)
+    assert g.status[1] == 0
+    np.testing.assert_allclose(g.field("dx")[1], o.field("dx")[1], rtol=0, atol=1e-9 * np.abs(o.field("dx")[1]).max())
+
+
+def test_gpu_summary_and_device_inputs(eng, oracle_lib):
+    import torch
+    from mim_solvers_b200.problems import make_random_batch
+    batch = make_random_batch(7, 12, 12, 6)
+    g = eng(shape=batch.shape())
+    dev = {k: torch.from_numpy(v).cuda() for k, v in batch.arrays.items()}
+    g.attach_device(dev)
+    g.sqp_direction()
+    o = oracle_lib.Oracle(batch); o.sqp_direction()
+    s = g.summary(1e-6)
+    assert abs(s["max_kkt"] - o.scalar("KKT").max()) <= 1e-9 * o.scalar("KKT").max()
+    assert s["n_failed"] == 0 and s["sum_qp_iters"] == 0
+    assert g.launch_count >= 2
