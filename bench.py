@@ -1,0 +1,385 @@
+#!/usr/bin/env python
+"""bench.py -- OCP QP solves/s of the batched computeDirection hot path on B200.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl reference]
+
+A "step" is one pass of the hot path (one `computeDirection` per problem) over one batch
+of synthetic derivatives.  Default workload = BASELINE.json configs[1]: UR5-shaped SQP
+(nx=12, nu=6, T=100), B=4096 problems per GPU (weak scaling, no data-path collective; the
+only collective is the all-reduce of the 5-number batch summary).
+
+Printed JSON (one line, rank 0):
+  value     QP solves/s, device-resident inputs, K back-to-back launches, CUDA events,
+            barrier + synchronize on both sides, max over ranks
+  e2e       same metric through the C ABI with HOST (pinned) buffers: H2D of the step's
+            derivatives and D2H of dx/du/lag_mul + scalars inside the timed region
+  roofline  algorithmic bytes (SURVEY 8d bytes_QP x B) / mean kernel time vs measured HBM
+  cpu_baseline  the CPU oracle (a port of the reference's Eigen code, see oracle/) on a
+            bounded sample of the same workload on this box's host cores
+`--impl reference` times that CPU implementation alone (the reference itself cannot be
+built here: Eigen/Boost/crocoddyl are absent).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+from mim_solvers_b200 import _capi  # noqa: E402
+from mim_solvers_b200.problems import CONFIGS, OCPBatch, make_config, tile_batch  # noqa: E402
+
+METRIC = "OCP QP solves/sec (batched FP64 Riccati+ADMM)"
+UNIT = "QP/s"
+
+# workload -> (solver, per-GPU batch, CSQP protocol)
+WORKLOADS = {
+    "C2_ur5_sqp": dict(solver="sqp", B=4096),
+    "C1_ur5_sqp": dict(solver="sqp", B=4096),
+    "C1_ur5_csqp": dict(solver="csqp", B=4096),
+    "C3_solo12_csqp": dict(solver="csqp", B=2048),
+    "C3b_solo12_bench": dict(solver="csqp", B=2048),
+    "C4_lq_nx64": dict(solver="sqp", B=1024),
+    "C4_clq_nx64": dict(solver="csqp", B=256),
+    "C4_lq_nx32": dict(solver="sqp", B=4096),
+    "C4_clq_nx32": dict(solver="csqp", B=1024),
+    "C4_lq_nx16": dict(solver="sqp", B=4096),
+    "C4_lq_nx8": dict(solver="sqp", B=4096),
+    "C5_talos_csqp": dict(solver="csqp", B=512),
+    "C5_talos_sqp": dict(solver="sqp", B=512),
+}
+
+
+def csqp_bench_params():
+    """benchmarks/solo12.cpp:213-216: eps_abs = eps_rel = 0, max_qp_iters = 50, no
+    equality-QP initial guess -> exactly 50 ADMM iterations per QP."""
+    return _capi.default_csqp_params(eps_abs=0.0, eps_rel=0.0, max_qp_iters=50,
+                                     equality_qp_initial_guess=0)
+
+
+def make_workload(name: str, B: int, first: int, distinct: int) -> OCPBatch:
+    """B problems; the first `distinct` are drawn independently (seed 5489 + index), the rest
+    repeat them (timing of these kernels does not depend on the data values)."""
+    d = min(B, distinct)
+    base = make_config(name, d, first=first)
+    return base if d == B else tile_batch(base, B)
+
+
+# ------------------------------------------------------------------ clocks sampler
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device: int):
+        self.device, self.rows, self._stop, self._t = device, [], threading.Event(), None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.device), f"--query-gpu={self.Q}",
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True,
+                                     timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([c.strip() for c in out.split(",")])
+            except Exception:
+                pass
+            self._stop.wait(0.1)
+
+    def __enter__(self):
+        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        self._t.join(timeout=6)
+
+    def summary(self):
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unavailable"]}
+        sm = sorted(float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(r[3 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": float(self.rows[0][1]),
+                "power_w_max": max(float(r[2]) for r in self.rows), "samples": len(self.rows), "reasons": reasons}
+
+
+# ------------------------------------------------------------------ CPU arm (oracle)
+def _oracle_native():
+    """Build the oracle with -O3 -march=native ON THIS BOX (the portable build travels
+    with the snapshot; a native one must not) and return the module bound to it."""
+    from oracle import oracle
+    out = ROOT / "oracle" / "_build" / "libmim_oracle_native.so"
+    src = ROOT / "oracle" / "mim_oracle.c"
+    try:
+        if not out.exists() or out.stat().st_mtime < src.stat().st_mtime:
+            out.parent.mkdir(exist_ok=True)
+            subprocess.run(["gcc", "-O3", "-march=native", "-std=c11", "-fPIC", "-fopenmp", "-shared", "-o",
+                            str(out), str(src), "-lm"], check=True, capture_output=True)
+        oracle._LIB_PATH = out
+        oracle._lib = None
+    except Exception:
+        oracle.build()
+    return oracle
+
+
+def cpu_run(workload: str, solver: str, sample_B: int, steps: int, warmup: int, nthreads: int = 0):
+    """Times the oracle's computeDirection over `sample_B` problems, all host threads."""
+    oracle = _oracle_native()
+    batch = make_workload(workload, sample_B, 0, distinct=min(sample_B, 64))
+    o = oracle.Oracle(batch, nthreads=nthreads)
+    cores = oracle.max_threads() if nthreads <= 0 else nthreads
+    if solver == "csqp":
+        p = csqp_bench_params()
+        o.csqp_calc_norms()
+        o.csqp_reset_rho(p)
+        call = lambda: o.csqp_direction(p, with_kkt=True)
+    else:
+        p = _capi.default_sqp_params()
+        call = lambda: o.sqp_direction(p, with_kkt=True)
+    for _ in range(warmup):
+        call()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        call()
+    dt = (time.perf_counter() - t0) / steps
+    return dict(value=sample_B / dt, ms_per_step=dt * 1e3, cores=cores, sample_B=sample_B)
+
+
+def pick_cpu_sample(workload: str, solver: str, target_s: float = 1.5) -> int:
+    """Sample size so that one CPU step is about `target_s` seconds."""
+    probe = cpu_run(workload, solver, 8, 1, 1)
+    per_qp_all_cores = 1.0 / probe["value"]
+    n = int(max(8, min(4096, target_s / per_qp_all_cores)))
+    return max(8, (n // 8) * 8)
+
+
+def reference_arm(args, rank, world):
+    if rank != 0:
+        return
+    w = WORKLOADS[args.workload]
+    sample = pick_cpu_sample(args.workload, w["solver"])
+    r = cpu_run(args.workload, w["solver"], sample, max(1, args.steps), max(1, args.warmup))
+    cfg = dict(CONFIGS[args.workload])
+    line = {
+        "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": args.workload, "solver": w["solver"], **cfg, "B_per_step": sample},
+        "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",
+                         "sample": f"{sample} problems of {args.workload} per step, oracle -O3 -march=native, "
+                                   f"OpenMP over problems"},
+        "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "note": "reference C++ unbuildable here (Eigen/Boost/crocoddyl absent): CPU oracle port timed instead",
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------ GPU arm
+def gpu_arm(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    from mim_solvers_b200.engine import BatchEngine
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    w = WORKLOADS[args.workload]
+    solver, B = w["solver"], (args.batch or w["B"])
+    cfg = dict(CONFIGS[args.workload])
+    batch = make_workload(args.workload, B, first=rank * B, distinct=args.distinct)
+    stream = torch.cuda.current_stream(dev)
+    shape = batch.shape()
+
+    # --- device-resident arm: inputs live in HBM before the timed region
+    eng = BatchEngine(shape=shape, device=local_rank, stream=stream.cuda_stream)
+    dev_in = {k: torch.from_numpy(v).to(dev) for k, v in batch.arrays.items()}
+    eng.attach_device(dev_in)
+    if solver == "csqp":
+        p = csqp_bench_params()
+        eng.csqp_calc_norms()
+        eng.csqp_reset_rho(p)
+        step = lambda: eng.csqp_direction(p, with_kkt=True)
+    else:
+        p = _capi.default_sqp_params()
+        step = lambda: eng.sqp_direction(p, with_kkt=True)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    l0 = eng.launch_count
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    with ClockSampler(local_rank) as clk:
+        barrier()
+        evs[0].record(stream)
+        for i in range(args.steps):
+            step()
+            evs[i + 1].record(stream)
+        barrier()
+    launches = eng.launch_count - l0
+    per = [evs[i].elapsed_time(evs[i + 1]) for i in range(args.steps)]
+    total_ms = evs[0].elapsed_time(evs[-1])
+    summ = eng.summary(1e-6)
+    tt = torch.tensor([total_ms], dtype=torch.float64, device=dev)
+    red = torch.tensor([summ["max_kkt"], float(summ["sum_qp_iters"]), float(summ["n_converged"]),
+                        float(summ["n_failed"])], dtype=torch.float64, device=dev)
+    if world > 1:  # the only collectives -- max time, batch-wide summary
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        mk = red[:1].clone()
+        dist.all_reduce(mk, op=dist.ReduceOp.MAX)
+        dist.all_reduce(red, op=dist.ReduceOp.SUM)
+        red[0] = mk[0]
+    total_ms = float(tt.item())
+    ms_per_step = total_ms / args.steps
+    value = world * B / (ms_per_step * 1e-3)
+
+    # --- roofline of the dominant kernel (one launch per step)
+    peaks_file = ROOT / "MEASURED_PEAKS.json"
+    if peaks_file.exists():
+        hbm_peak, peak_src = float(json.loads(peaks_file.read_text())["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs"
+    else:
+        hbm_peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    kernel_ms = float(np.mean(per))
+    bytes_qp = batch.algorithmic_bytes_per_qp()
+    flops_qp = batch.flops_csqp_qp(50, False) if solver == "csqp" else batch.flops_sqp_qp()
+    ach_gbs = bytes_qp * B / (kernel_ms * 1e-3) / 1e9
+    roof = {"bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": ach_gbs / hbm_peak,
+            "traffic": None, "peak_source": peak_src, "kernel_ms": kernel_ms,
+            "algorithmic_bytes_per_qp": bytes_qp, "flops_per_qp": flops_qp,
+            "fp64_tflops_achieved": flops_qp * B / (kernel_ms * 1e-3) / 1e12}
+    if solver == "csqp" or flops_qp / bytes_qp > 36.8e12 / (hbm_peak * 1e9):
+        roof.update(bound="fp64", achieved=roof["fp64_tflops_achieved"], peak=36.8, unit="TFLOP/s",
+                    frac=roof["fp64_tflops_achieved"] / 36.8,
+                    peak_source="mimgpu_measure_peaks DFMA loop on B200 (profiles/peaks_r01.json)")
+
+    # --- end-to-end arm: host (pinned) buffers through the C ABI, copies inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        del dev_in
+        eng.close()
+        torch.cuda.empty_cache()
+        eng2 = BatchEngine(shape=shape, device=local_rank, stream=stream.cuda_stream)
+        pinned = OCPBatch(batch.B, batch.T, batch.nx, batch.nu, batch.ng, batch.ngT)
+        for k, v in batch.arrays.items():
+            t = torch.empty(v.shape, dtype=torch.float64).pin_memory()
+            t.numpy()[...] = v
+            pinned.arrays[k] = t.numpy()
+            pinned.arrays["_t_" + k] = t
+        keep = {k: pinned.arrays.pop(k) for k in list(pinned.arrays) if k.startswith("_t_")}
+        outs = {n: torch.empty(tuple(shape.field_shape(n)), dtype=torch.float64).pin_memory()
+                for n in (("dx_tilde", "du_tilde", "lag_mul", "y", "z") if solver == "csqp"
+                          else ("dx", "du", "lag_mul"))}
+        kkt = torch.empty(B, dtype=torch.float64).pin_memory()
+        h2d = sum(v.nbytes for v in pinned.arrays.values())
+        d2h = sum(t.numel() * 8 for t in outs.values()) + B * 8
+
+        def e2e_step():
+            eng2.upload(pinned)
+            if solver == "csqp":
+                eng2.csqp_calc_norms()
+                eng2.csqp_reset_rho(p)
+                eng2.csqp_direction(p, with_kkt=True)
+            else:
+                eng2.sqp_direction(p, with_kkt=True)
+            for n, t in outs.items():
+                if t.numel():
+                    eng2.download_into(n, t.numpy())
+            _capi.check(eng2._lib.mimgpu_scalar(eng2._ctx, _capi.SCALARS["KKT"], kkt.numpy().ctypes.data,
+                                               eng2.stream), "mimgpu_scalar")
+            eng2.sync()
+
+        n_e2e = max(2, min(args.steps, args.e2e_steps))
+        for _ in range(2):
+            e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(n_e2e):
+            e2e_step()
+        barrier()
+        dt = torch.tensor([(time.perf_counter() - t0) / n_e2e], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        launches_e2e = eng2.launch_count
+        e2e = {"value": world * B / float(dt.item()), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+               "d2h_bytes_per_step": int(d2h), "ms_per_step": float(dt.item()) * 1e3, "steps": n_e2e,
+               "max_kkt": float(kkt.max())}
+        del keep
+
+    if rank != 0:
+        return
+    cpu = None
+    if not args.no_cpu:
+        sample = pick_cpu_sample(args.workload, solver, target_s=1.0)
+        r = cpu_run(args.workload, solver, sample, 10, 2)
+        cpu = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",
+               "sample": f"{sample} problems of {args.workload} x 10 passes, CPU oracle (-O3 -march=native, "
+                         f"OpenMP over problems)"}
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": args.workload, "solver": solver, **cfg, "B_per_gpu": B,
+                   "distinct_problems_per_gpu": min(B, args.distinct),
+                   "l2": f"inputs {batch.nbytes() / 1e6:.0f} MB per step > 126 MB L2 (no flush needed)"
+                         if batch.nbytes() > 2 * 126e6 else "inputs smaller than 2x L2",
+                   "csqp_protocol": "eps_abs=eps_rel=0, 50 ADMM iterations, no eq. guess" if solver == "csqp" else None},
+        "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
+        "clocks": clk.summary(),
+        "batch_summary": {"max_kkt": float(red[0]), "sum_qp_iters": int(red[1]), "n_converged": int(red[2]),
+                          "n_failed": int(red[3])},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="C2_ur5_sqp", choices=sorted(WORKLOADS))
+    ap.add_argument("--batch", type=int, default=0, help="problems per GPU (default: the workload's)")
+    ap.add_argument("--distinct", type=int, default=4096, help="independently drawn problems per GPU")
+    ap.add_argument("--e2e-steps", type=int, default=5)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        reference_arm(args, rank, world)
+        return
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    try:
+        gpu_arm(args, rank, world, local_rank)
+    finally:
+        if world > 1:
+            import torch.distributed as dist
+            dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
