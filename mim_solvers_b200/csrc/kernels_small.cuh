@@ -1,7 +1,21 @@
 /*
- * kernels_small.cuh -- specialised kernels for the small hot shapes (UR5 class).
- * Placeholder interface: until a specialisation is registered the generic kernels
- * (kernels_generic.cuh) serve every shape.
+ * kernels_small.cuh -- warp-per-problem SQP direction kernel for small shapes
+ * (UR5 class: nx = 12, nu = 6; any even NX, NU with NX + 2 NU <= 32).
+ *
+ * Replaces, in ONE launch: SolverDDP::backwardPass + computeGains (src/ddp.cpp:265-348,
+ * 401-429), SolverSQP::forwardPass (src/sqp.cpp:270-305), checkKKTConditions
+ * (src/sqp.cpp:244-268) and the gap norm / merit of computeDirection (src/sqp.cpp:229-236).
+ *
+ * Mapping.  One warp owns one problem; all sizes are compile-time so every matrix lives
+ * in registers as "one column per lane":
+ *   lanes [0, NX)        column j of Fx   -> W = Vxx' Fx,  Qxx column j, Vxx column j, K column j
+ *   lanes [NX, N)        column a of Fu   -> W = Vxx' Fu,  Quu column a
+ *   lanes [N, N + NU)    column a of Fu   -> (duplicate W)  Qxu column a
+ * The operand every lane needs in common (Vxx', [Fx Fu], Qxu) is read from shared memory
+ * as a warp-wide broadcast (one wavefront per 16-byte load).  The 6x6 Cholesky and the
+ * triangular solves are done redundantly per lane in registers (no cross-lane traffic).
+ * Each knot's derivative blocks are staged global -> shared with cp.async one knot ahead
+ * (double buffer), so the HBM latency of knot t-1 hides behind the arithmetic of knot t.
  */
 #pragma once
 #include <cuda_runtime.h>
@@ -10,10 +24,513 @@
 
 namespace mimgpu {
 
-/* returns 1 when a specialised SQP kernel exists for this shape */
-static inline int small_kernels_configure(const mimgpu_shape&) { return 0; }
+template <int NX, int NU>
+struct SmallCfg {
+  static constexpr int N = NX + NU;
+  static constexpr int LDQ = NX + 2;  /* leading dim of the shared Qxu (+ Qu row) block */
+  /* backward stage: [Fx|Fu] [Lxx|Lxu] Luu [Lx|Lu] fs */
+  static constexpr int bF = 0, bH = NX * N, bLuu = 2 * NX * N, bL = bLuu + NU * NU, bFs = bL + N,
+                       STAGE_B = bFs + NX;
+  /* forward stage: Vxx+ Vx+ K k [Fx|Fu] fs+ [Lx|Lu] */
+  static constexpr int fV = 0, fVx = NX * NX, fK = fVx + NX, fk = fK + NX * NU, fF = fk + NU, fFs = fF + NX * N,
+                       fL = fFs + NX, STAGE_F = fL + N;
+  static constexpr int STAGE = (STAGE_B > STAGE_F ? STAGE_B : STAGE_F);
+  /* per-warp shared memory (doubles) */
+  static constexpr int oS0 = 0, oS1 = STAGE, oV = 2 * STAGE, oT = oV + NX * NX, oQxu = oT + NX * NX,
+                       oQuu = oQxu + LDQ * NU + 32, oVx = oQuu + NU * NU, oK = oVx + NX, oX = oK + NU,
+                       oU = oX + NX, oXn = oU + NU, oLam = oXn + NX, WARP = oLam + NX + 2;
+  static_assert(NX % 2 == 0 && NU % 2 == 0, "16-byte staging needs even block sizes");
+  static_assert(N + NU <= 32, "one column per lane");
+};
 
-/* returns 0 when launched, < 0 when no specialisation applies, > 0 on error */
-static inline int small_sqp_direction_launch(const KArgs&, const SqpKPar&, int, cudaStream_t) { return -1; }
+__device__ __forceinline__ void cp_async16(double* smem_dst, const double* gsrc) {
+  const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int NPEND>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(NPEND) : "memory");
+}
+/* warp-cooperative copy of NDBL doubles (even, 16-byte aligned on both sides) */
+template <int NDBL>
+__device__ __forceinline__ void warp_stage(double* dst, const double* src, int lane) {
+  static_assert(NDBL % 2 == 0, "even");
+#pragma unroll
+  for (int c = 0; c < (NDBL / 2 + 31) / 32; ++c) {
+    const int i = lane + 32 * c;
+    if (i < NDBL / 2) cp_async16(dst + 2 * i, src + 2 * i);
+  }
+}
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ double warp_nmax(double v) {
+#pragma unroll
+  for (int o = 16; o; o >>= 1) v = nmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+/* ------------------------------------------------------------------ backward */
+/* Returns the status word (uniform over the warp). */
+template <int NX, int NU>
+__device__ __forceinline__ int small_backward(const Prob& p, double* sw, int lane, double preg, double dreg,
+                                              int is_feasible) {
+  using C = SmallCfg<NX, NU>;
+  constexpr int N = C::N, LDQ = C::LDQ;
+  const int T = p.T;
+  double* sV = sw + C::oV;
+  double* sT = sw + C::oT;
+  double* sQxu = sw + C::oQxu;
+  double* sQuu = sw + C::oQuu;
+  double* sVx = sw + C::oVx;
+  double* sK = sw + C::oK;
+  const bool gxx = lane < NX, guu = lane >= NX && lane < N, gxu = lane >= N && lane < N + NU;
+  const int col = lane < N ? lane : (gxu ? lane - NU : 0);
+  const int ua = guu ? lane - NX : (gxu ? lane - N : 0);
+  const int rr = lane <= NX ? lane : 0;   /* rhs row of the gain solve */
+  const int lx = gxx ? lane : 0;
+
+  auto prefetch = [&](int t, double* st) {
+    warp_stage<NX * NX>(st + C::bF, p.Fx + (size_t)t * NX * NX, lane);
+    warp_stage<NX * NU>(st + C::bF + NX * NX, p.Fu + (size_t)t * NX * NU, lane);
+    warp_stage<NX * NX>(st + C::bH, p.Lxx + (size_t)t * NX * NX, lane);
+    warp_stage<NX * NU>(st + C::bH + NX * NX, p.Lxu + (size_t)t * NX * NU, lane);
+    warp_stage<NU * NU>(st + C::bLuu, p.Luu + (size_t)t * NU * NU, lane);
+    warp_stage<NX>(st + C::bL, p.Lx + (size_t)t * NX, lane);
+    warp_stage<NU>(st + C::bL + NX, p.Lu + (size_t)t * NU, lane);
+    warp_stage<NX>(st + C::bFs, p.fs + (size_t)t * NX, lane);
+    cp_async_commit();
+  };
+  prefetch(T - 1, sw + C::oS0);
+
+  /* ---- terminal knot (src/ddp.cpp:268-277).  sV holds Vxx_T TRANSPOSED so that the
+   * first sweep uses Vxx_T[m,k] exactly as the reference does even if Lxx_T is not
+   * bitwise symmetric; every later Vxx is symmetrised. */
+  {
+    double v[NX];
+#pragma unroll
+    for (int i = 0; i < NX; i += 2) {
+      const double2 t2 = *reinterpret_cast<const double2*>(p.LxxT + NX * lx + i);
+      v[i] = t2.x; v[i + 1] = t2.y;
+    }
+    if (!isnan(preg)) {
+#pragma unroll
+      for (int i = 0; i < NX; ++i) if (i == lx) v[i] += preg;
+    }
+    if (gxx) {
+#pragma unroll
+      for (int i = 0; i < NX; ++i) sV[lane + NX * i] = v[i];       /* sV[j + NX i] = Vxx_T[i, j] */
+#pragma unroll
+      for (int i = 0; i < NX; i += 2)
+        *reinterpret_cast<double2*>(p.Vxx + (size_t)T * NX * NX + NX * lane + i) = make_double2(v[i], v[i + 1]);
+    }
+    __syncwarp();
+    double vx = p.LxT[lx];
+    if (!is_feasible) {
+      double acc = 0.0;
+#pragma unroll
+      for (int j = 0; j < NX; ++j) acc = fma(sV[j + NX * lx], p.fs[(size_t)T * NX + j], acc); /* Vxx_T[lx, j] */
+      vx += acc;
+    }
+    if (gxx) { sVx[lane] = vx; p.Vx[(size_t)T * NX + lane] = vx; }
+    __syncwarp();
+  }
+
+  int s = 0;
+  for (int t = T - 1; t >= 0; --t) {
+    double* st = sw + (s ? C::oS1 : C::oS0);
+    if (t > 0) {
+      prefetch(t - 1, sw + (s ? C::oS0 : C::oS1));
+      cp_async_wait<1>();
+    } else {
+      cp_async_wait<0>();
+    }
+    __syncwarp();
+
+    /* ---- step 1: w = Vxx' F[:, col]  (= row `col` of FxTVxx / FuTVxx, src/ddp.cpp:289,299)
+     *      and qv = [Lx; Lu][col] + F[:, col] . Vx'  (src/ddp.cpp:291-292, 301-302) */
+    double f[NX], w[NX];
+#pragma unroll
+    for (int i = 0; i < NX; i += 2) {
+      const double2 t2 = *reinterpret_cast<const double2*>(st + C::bF + NX * col + i);
+      f[i] = t2.x; f[i + 1] = t2.y;
+      w[i] = 0.0; w[i + 1] = 0.0;
+    }
+    double qv = 0.0;
+#pragma unroll
+    for (int m = 0; m < NX; ++m) {
+#pragma unroll
+      for (int k = 0; k < NX; k += 2) {
+        const double2 v2 = *reinterpret_cast<const double2*>(sV + NX * m + k);
+        w[k] = fma(v2.x, f[m], w[k]);
+        w[k + 1] = fma(v2.y, f[m], w[k + 1]);
+      }
+      qv = fma(f[m], sVx[m], qv);
+    }
+    qv = st[C::bL + col] + qv;
+
+    /* ---- step 2: Q[i, col] = H[i, col] + sum_k F[k, i] w[k]  (src/ddp.cpp:295-314) */
+    double q[NX];
+    {
+      const double* fb = st + C::bF + (guu ? NX * NX : 0);
+      const double* hp = guu ? st + C::bLuu + NU * ua : st + C::bH + NX * col;
+#pragma unroll
+      for (int r = 0; r < NX; r += 2) {
+        double a0 = 0.0, a1 = 0.0;
+#pragma unroll
+        for (int k = 0; k < NX; k += 2) {
+          const double2 f0 = *reinterpret_cast<const double2*>(fb + NX * r + k);
+          const double2 f1 = *reinterpret_cast<const double2*>(fb + NX * (r + 1) + k);
+          a0 = fma(f0.x, w[k], a0); a0 = fma(f0.y, w[k + 1], a0);
+          a1 = fma(f1.x, w[k], a1); a1 = fma(f1.y, w[k + 1], a1);
+        }
+        const double2 h2 = *reinterpret_cast<const double2*>(hp + r);
+        q[r] = h2.x + a0; q[r + 1] = h2.y + a1;
+      }
+    }
+    if (guu && !isnan(dreg)) {
+#pragma unroll
+      for (int r = 0; r < NU; ++r) if (r == ua) q[r] += dreg;
+    }
+    /* ---- publish Quu, Qxu, Qu */
+    if (guu) {
+#pragma unroll
+      for (int r = 0; r < NU; ++r) sQuu[r + NU * ua] = q[r];
+      sQxu[NX + LDQ * ua] = qv;                       /* Qu[ua] */
+      p.Qu[(size_t)t * NU + ua] = qv;
+    }
+    if (gxu) {
+#pragma unroll
+      for (int r = 0; r < NX; ++r) sQxu[r + LDQ * ua] = q[r];
+    }
+    __syncwarp();
+
+    /* ---- computeGains (src/ddp.cpp:401-429): Cholesky redundantly in every lane */
+    double Lm[NU][NU], inv[NU];
+#pragma unroll
+    for (int j = 0; j < NU; ++j)
+#pragma unroll
+      for (int i = j; i < NU; ++i) Lm[i][j] = sQuu[i + NU * j];
+    bool llt_fail = false;
+#pragma unroll
+    for (int k = 0; k < NU; ++k) {
+      double x = Lm[k][k];
+#pragma unroll
+      for (int j = 0; j < k; ++j) x = fma(-Lm[k][j], Lm[k][j], x);
+      if (x <= 0.0) llt_fail = true;
+      const double ri = rsqrt(x);
+      Lm[k][k] = x * ri;
+      inv[k] = ri;
+#pragma unroll
+      for (int i = k + 1; i < NU; ++i) {
+        double v = Lm[i][k];
+#pragma unroll
+        for (int j = 0; j < k; ++j) v = fma(-Lm[i][j], Lm[k][j], v);
+        Lm[i][k] = v * ri;
+      }
+    }
+    if (llt_fail) return MIMGPU_STATUS_LLT | (t << 8);
+    double kc[NU];                                    /* K[:, lane] (lane < NX) or k (lane == NX) */
+#pragma unroll
+    for (int a = 0; a < NU; ++a) kc[a] = sQxu[rr + LDQ * a];
+#pragma unroll
+    for (int i = 0; i < NU; ++i) {
+      double v = kc[i];
+#pragma unroll
+      for (int j = 0; j < i; ++j) v = fma(-Lm[i][j], kc[j], v);
+      kc[i] = v * inv[i];
+    }
+#pragma unroll
+    for (int i = NU - 1; i >= 0; --i) {
+      double v = kc[i];
+#pragma unroll
+      for (int j = i + 1; j < NU; ++j) v = fma(-Lm[j][i], kc[j], v);
+      kc[i] = v * inv[i];
+    }
+    if (gxx) {
+#pragma unroll
+      for (int a = 0; a < NU; ++a) p.K[(size_t)t * NX * NU + a * NX + lane] = kc[a];
+    }
+    if (lane == NX) {
+#pragma unroll
+      for (int a = 0; a < NU; ++a) { sK[a] = kc[a]; p.kff[(size_t)t * NU + a] = kc[a]; }
+    }
+    if (lane == NX + 1) {                              /* Quu_llt_[t]: lower factor, upper part zero */
+#pragma unroll
+      for (int c = 0; c < NU; ++c)
+#pragma unroll
+        for (int r = 0; r < NU; r += 2)
+          *reinterpret_cast<double2*>(p.L + (size_t)t * NU * NU + NU * c + r) =
+              make_double2(r >= c ? Lm[r][c] : 0.0, r + 1 >= c ? Lm[r + 1][c] : 0.0);
+    }
+    __syncwarp();
+    if (lane < NU) {                                  /* Quuk = Quu k  (src/ddp.cpp:322) */
+      double acc = 0.0;
+#pragma unroll
+      for (int c = 0; c < NU; ++c) acc = fma(sQuu[lane + NU * c], sK[c], acc);
+      p.Quuk[(size_t)t * NU + lane] = acc;
+    }
+    /* ---- value function (src/ddp.cpp:319-338) */
+    double vx;
+    {
+      double acc = 0.0;
+#pragma unroll
+      for (int a = 0; a < NU; ++a) acc = fma(kc[a], sQxu[NX + LDQ * a], acc);
+      vx = qv - acc;
+    }
+#pragma unroll
+    for (int i = 0; i < NX; i += 2) {
+      double a0 = 0.0, a1 = 0.0;
+#pragma unroll
+      for (int a = 0; a < NU; ++a) {
+        const double2 x2 = *reinterpret_cast<const double2*>(sQxu + LDQ * a + i);
+        a0 = fma(x2.x, kc[a], a0);
+        a1 = fma(x2.y, kc[a], a1);
+      }
+      q[i] -= a0; q[i + 1] -= a1;
+    }
+    if (gxx) {
+#pragma unroll
+      for (int i = 0; i < NX; i += 2) *reinterpret_cast<double2*>(sT + NX * lane + i) = make_double2(q[i], q[i + 1]);
+    }
+    __syncwarp();
+    bool bad = false;
+    {
+      double acc = 0.0;
+#pragma unroll
+      for (int i = 0; i < NX; ++i) {
+        double v = 0.5 * (q[i] + sT[lx + NX * i]);
+        if (i == lx && !isnan(preg)) v += preg;
+        q[i] = v;
+        acc = fma(v, st[C::bFs + i], acc);
+        bad |= raise_if_nan(fabs(v));
+      }
+      if (!is_feasible) vx += acc;
+      bad |= raise_if_nan(fabs(vx));
+    }
+    if (gxx) {
+#pragma unroll
+      for (int i = 0; i < NX; i += 2) {
+        const double2 v2 = make_double2(q[i], q[i + 1]);
+        *reinterpret_cast<double2*>(sV + NX * lane + i) = v2;
+        *reinterpret_cast<double2*>(p.Vxx + (size_t)t * NX * NX + NX * lane + i) = v2;
+      }
+      sVx[lane] = vx;
+      p.Vx[(size_t)t * NX + lane] = vx;
+    }
+    if (__any_sync(0xffffffffu, bad && gxx)) return MIMGPU_STATUS_NONFINITE | (t << 8);
+    __syncwarp();
+    s ^= 1;
+  }
+  return 0;
+}
+
+/* ------------------------------------------------------------------- forward */
+/* SolverSQP::forwardPass + checkKKTConditions + gap norm (src/sqp.cpp:270-305, 244-268,
+ * 229-236).  Lane i < NX owns state row i, lane a < NU control row a, lane c < N column c
+ * of [Fx Fu] for the stationarity residual. */
+template <int NX, int NU>
+__device__ __forceinline__ void small_forward(const Prob& p, double* sw, int lane, double mu_dynamic) {
+  using C = SmallCfg<NX, NU>;
+  constexpr int N = C::N;
+  const int T = p.T;
+  double* sX = sw + C::oX;
+  double* sU = sw + C::oU;
+  double* sXn = sw + C::oXn;
+  double* sLam = sw + C::oLam;
+  const bool gx = lane < NX, gu = lane < NU, gc = lane < N;
+  const int lx = gx ? lane : 0, lu = gu ? lane : 0, lc = gc ? lane : 0;
+
+  auto prefetch = [&](int t, double* st) {
+    warp_stage<NX * NX>(st + C::fV, p.Vxx + (size_t)(t + 1) * NX * NX, lane);
+    warp_stage<NX>(st + C::fVx, p.Vx + (size_t)(t + 1) * NX, lane);
+    warp_stage<NX * NU>(st + C::fK, p.K + (size_t)t * NX * NU, lane);
+    warp_stage<NU>(st + C::fk, p.kff + (size_t)t * NU, lane);
+    warp_stage<NX * NX>(st + C::fF, p.Fx + (size_t)t * NX * NX, lane);
+    warp_stage<NX * NU>(st + C::fF + NX * NX, p.Fu + (size_t)t * NX * NU, lane);
+    warp_stage<NX>(st + C::fFs, p.fs + (size_t)(t + 1) * NX, lane);
+    warp_stage<NX>(st + C::fL, p.Lx + (size_t)t * NX, lane);
+    warp_stage<NU>(st + C::fL + NX, p.Lu + (size_t)t * NU, lane);
+    cp_async_commit();
+  };
+  __syncwarp();                 /* the backward pass' global stores are ordered before these reads */
+  prefetch(0, sw + C::oS0);
+
+  double xg = 0.0, ug = 0.0, gap = 0.0, kkt = 0.0;
+  /* knot 0: dx_0 (member, stays 0), lag_mul_0 = Vxx_0 (dx_0 - fs_0) + Vx_0 */
+  double fs_cur = p.fs[lx];
+  double x_cur = p.dx[lx];
+  if (gx) sX[lane] = x_cur - fs_cur;
+  __syncwarp();
+  double lam;
+  {
+    double acc = 0.0;
+#pragma unroll
+    for (int j = 0; j < NX; ++j) acc = fma(p.Vxx[lx + NX * j], sX[j], acc);
+    lam = acc + p.Vx[lx];
+    if (gx) p.lag[lane] = lam;
+  }
+  __syncwarp();
+  if (gx) sX[lane] = x_cur;
+  __syncwarp();
+
+  int s = 0;
+  for (int t = 0; t < T; ++t) {
+    const double* st = sw + (s ? C::oS1 : C::oS0);
+    if (t + 1 < T) {
+      prefetch(t + 1, sw + (s ? C::oS0 : C::oS1));
+      cp_async_wait<1>();
+    } else {
+      cp_async_wait<0>();
+    }
+    __syncwarp();
+    if (gx) { xg += fabs(x_cur); gap += fabs(fs_cur); kkt = nmax(kkt, fabs(fs_cur)); }
+    /* du = -K dx - k  (src/sqp.cpp:285-286) */
+    {
+      double acc = 0.0;
+#pragma unroll
+      for (int i = 0; i < NX; i += 2) {
+        const double2 k2 = *reinterpret_cast<const double2*>(st + C::fK + NX * lu + i);
+        acc = fma(k2.x, sX[i], acc);
+        acc = fma(k2.y, sX[i + 1], acc);
+      }
+      double v = -acc;
+      v -= st[C::fk + lu];
+      if (gu) { sU[lane] = v; p.du[(size_t)t * NU + lane] = v; ug += fabs(v); }
+    }
+    __syncwarp();
+    /* dx+ = fs+ + Fu du + Fx dx  (src/sqp.cpp:287-289) */
+    const double fs_n = st[C::fFs + lx];
+    double x_n;
+    {
+      double acc = 0.0;
+#pragma unroll
+      for (int a = 0; a < NU; ++a) acc = fma(st[C::fF + NX * NX + lx + NX * a], sU[a], acc);
+      x_n = fs_n + acc;
+      acc = 0.0;
+#pragma unroll
+      for (int j = 0; j < NX; ++j) acc = fma(st[C::fF + lx + NX * j], sX[j], acc);
+      x_n += acc;
+      if (gx) { p.dx[(size_t)(t + 1) * NX + lane] = x_n; sXn[lane] = x_n - fs_n; }
+    }
+    __syncwarp();
+    /* lag_mul+ = Vxx+ (dx+ - fs+) + Vx+  (src/sqp.cpp:282-284, 296-298) */
+    double lam_n;
+    {
+      double acc = 0.0;
+#pragma unroll
+      for (int j = 0; j < NX; ++j) acc = fma(st[C::fV + lx + NX * j], sXn[j], acc);
+      lam_n = acc + st[C::fVx + lx];
+      if (gx) { p.lag[(size_t)(t + 1) * NX + lane] = lam_n; sLam[lane] = lam_n; }
+    }
+    __syncwarp();
+    /* stationarity rows of knot t  (src/sqp.cpp:249-258) */
+    {
+      double acc = 0.0;
+#pragma unroll
+      for (int k = 0; k < NX; k += 2) {
+        const double2 f2 = *reinterpret_cast<const double2*>(st + C::fF + NX * lc + k);
+        acc = fma(f2.x, sLam[k], acc);
+        acc = fma(f2.y, sLam[k + 1], acc);
+      }
+      double v = st[C::fL + lc] + acc;
+      if (gx) v -= lam;
+      if (gc) kkt = nmax(kkt, fabs(v));
+    }
+    if (gx) sX[lane] = x_n;
+    x_cur = x_n; fs_cur = fs_n; lam = lam_n;
+    __syncwarp();
+    s ^= 1;
+  }
+  if (gx) {
+    xg += fabs(x_cur); gap += fabs(fs_cur);
+    kkt = nmax(kkt, fabs(fs_cur));
+    kkt = nmax(kkt, fabs(p.LxT[lane] - lam));          /* src/sqp.cpp:259-262 */
+  }
+  xg = warp_sum(xg); ug = warp_sum(ug); gap = warp_sum(gap); kkt = warp_nmax(kkt);
+  if (lane == 0) {
+    const size_t B = p.B, b = p.b;
+    p.scal[MIMGPU_S_KKT * B + b] = kkt;
+    p.scal[MIMGPU_S_GAP_NORM * B + b] = gap;
+    p.scal[MIMGPU_S_MERIT * B + b] = p.cost + mu_dynamic * gap;
+    p.scal[MIMGPU_S_XGRAD_NORM * B + b] = xg / (double)(T + 1);
+    p.scal[MIMGPU_S_UGRAD_NORM * B + b] = ug / (double)T;
+  }
+}
+
+/* -------------------------------------------------------------------- kernel */
+template <int NX, int NU, int WPB>
+__global__ void __launch_bounds__(WPB * 32) k_sqp_direction_small(KArgs a, SqpKPar kp) {
+  extern __shared__ double smem_small[];
+  using C = SmallCfg<NX, NU>;
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int slot = blockIdx.x * WPB + wib;
+  if (slot >= a.n_active) return;
+  const int b = a.active ? a.active[slot] : slot;
+  double* sw = smem_small + (size_t)wib * C::WARP;
+  Prob p = bind(a, b);
+  const double preg = a.preg_arr ? a.preg_arr[b] : kp.preg;
+  const double dreg = a.dreg_arr ? a.dreg_arr[b] : kp.dreg;
+  const int st = small_backward<NX, NU>(p, sw, lane, preg, dreg, kp.is_feasible);
+  if (lane == 0) { a.status[b] = st; a.qp_iters[b] = 0; }
+  if (st) {
+    cp_async_wait<0>();
+    double gap = 0.0;
+    for (int e = lane; e < (p.T + 1) * NX; e += 32) gap += fabs(p.fs[e]);
+    gap = warp_sum(gap);
+    if (lane == 0) {
+      p.scal[MIMGPU_S_GAP_NORM * (size_t)p.B + b] = gap;
+      p.scal[MIMGPU_S_MERIT * (size_t)p.B + b] = p.cost + kp.mu_dynamic * gap;
+    }
+    return;
+  }
+  small_forward<NX, NU>(p, sw, lane, kp.mu_dynamic);
+}
+
+/* ------------------------------------------------------------------ dispatch */
+template <int NX, int NU, int WPB>
+static int small_launch_t(const KArgs& a, const SqpKPar& kp, cudaStream_t st, bool configure_only) {
+  using C = SmallCfg<NX, NU>;
+  const int smem = WPB * C::WARP * (int)sizeof(double);
+  auto kern = k_sqp_direction_small<NX, NU, WPB>;
+  if (configure_only) {
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return 1;
+    return 0;
+  }
+  const int grid = (a.n_active + WPB - 1) / WPB;
+  kern<<<grid, WPB * 32, smem, st>>>(a, kp);
+  return 0;
+}
+
+#define MIMGPU_SMALL_SHAPES(X) X(12, 6) X(8, 4) X(16, 8) X(4, 2) X(6, 2) X(10, 4)
+constexpr int kSmallWPB = 4;
+
+/* 1 when a specialised SQP kernel exists for this shape (and is configured) */
+static inline int small_kernels_configure(const mimgpu_shape& s) {
+  KArgs dummy{};
+  SqpKPar kp{};
+#define X(NX_, NU_) \
+  if (s.nx == NX_ && s.nu == NU_) return small_launch_t<NX_, NU_, kSmallWPB>(dummy, kp, nullptr, true) == 0;
+  MIMGPU_SMALL_SHAPES(X)
+#undef X
+  return 0;
+}
+
+/* 0 when launched, < 0 when no specialisation applies (caller uses the generic kernel) */
+static inline int small_sqp_direction_launch(const KArgs& a, const SqpKPar& kp, int, cudaStream_t st) {
+  /* cp.async needs 16-byte aligned sources: all blocks have even sizes, so only the base
+   * pointers matter */
+  const uintptr_t al = (uintptr_t)a.Fx | (uintptr_t)a.Fu | (uintptr_t)a.Lxx | (uintptr_t)a.Lxu | (uintptr_t)a.Luu |
+                       (uintptr_t)a.Lx | (uintptr_t)a.Lu | (uintptr_t)a.fs | (uintptr_t)a.LxxT;
+  if (al & 15) return -1;
+#define X(NX_, NU_) \
+  if (a.sh.nx == NX_ && a.sh.nu == NU_) return small_launch_t<NX_, NU_, kSmallWPB>(a, kp, st, false);
+  MIMGPU_SMALL_SHAPES(X)
+#undef X
+  return -1;
+}
 
 }  // namespace mimgpu

@@ -110,3 +110,36 @@ def test_gpu_summary_and_device_inputs(eng, oracle_lib):
     assert abs(s["max_kkt"] - o.scalar("KKT").max()) <= 1e-9 * o.scalar("KKT").max()
     assert s["n_failed"] == 0 and s["sum_qp_iters"] == 0
     assert g.launch_count >= 2
+
+
+@pytest.mark.parametrize("B,T,nx,nu", [(37, 25, 12, 6), (9, 7, 8, 4), (6, 5, 16, 8), (5, 30, 4, 2), (5, 9, 6, 2),
+                                       (7, 11, 10, 4)])
+def test_gpu_small_kernel_vs_oracle(eng, oracle_lib, B, T, nx, nu):
+    """Shapes served by the warp-per-problem kernel (kernels_small.cuh); ragged B (not a
+    multiple of the warps per CTA), feasible and infeasible variants."""
+    from mim_solvers_b200 import _capi
+    from mim_solvers_b200.problems import make_random_batch
+    batch = make_random_batch(B, T, nx, nu)
+    compare_engines_sqp(lambda b: eng(b), lambda b: oracle_lib.Oracle(b), batch)
+    compare_engines_sqp(lambda b: eng(b), lambda b: oracle_lib.Oracle(b), batch,
+                        params=_capi.default_sqp_params(preg=0.0, dreg=0.0, is_feasible=True))
+
+
+def test_gpu_small_kernel_failure_and_subset(eng, oracle_lib):
+    from mim_solvers_b200 import _capi
+    from mim_solvers_b200.problems import make_random_batch
+    batch = make_random_batch(6, 9, 12, 6)
+    batch.mat("Luu")[4, 3] = -10.0 * np.eye(6)
+    batch.mat("Lxx")[2, 6][0, 0] = np.nan
+    g, o = eng(batch), oracle_lib.Oracle(batch)
+    g.sqp_direction(); o.sqp_direction()
+    assert np.array_equal(g.status, np.asarray(o.status)), (g.status, np.asarray(o.status))
+    assert g.status[4] == (_capi.STATUS_LLT | (3 << 8)) and (g.status[2] & 0xff) == _capi.STATUS_NONFINITE
+    ok = g.status == 0
+    np.testing.assert_allclose(g.field("dx")[ok], o.field("dx")[ok], rtol=0, atol=1e-9 * np.abs(o.field("dx")[ok]).max())
+    g.set_active([4, 1])
+    preg = np.full(6, 1e-9); preg[4] = 30.0
+    g.sqp_direction(preg=preg, dreg=preg)
+    o.sqp_direction(preg=preg, dreg=preg)
+    assert g.status[4] == 0 and (g.status[2] & 0xff) == _capi.STATUS_NONFINITE   # problem 2 untouched
+    np.testing.assert_allclose(g.field("dx")[4], o.field("dx")[4], rtol=0, atol=1e-9 * np.abs(o.field("dx")[4]).max())
