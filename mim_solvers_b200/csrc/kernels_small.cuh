@@ -36,9 +36,15 @@ struct SmallCfg {
                        fL = fFs + NX, STAGE_F = fL + N;
   static constexpr int STAGE = (STAGE_B > STAGE_F ? STAGE_B : STAGE_F);
   /* per-warp shared memory (doubles) */
+  /* DMMA tiling: NT tiles of 8 over the N = NX + NU columns of [Fx Fu], XT over the NX states */
+  static constexpr int NT = (N + 7) / 8, XT = (NX + 7) / 8, KT = NX / 4, KPT = (NX + 1 + 7) / 8;
+  static constexpr int PC0 = 8 * (NX / 8);          /* first published column of Q */
+  static constexpr int LDP = 8 * NT - PC0 + 2;      /* leading dim of the published Q block */
+  static constexpr int LDK = 24;                    /* leading dim of the shared K (NU x NX) */
   static constexpr int oS0 = 0, oS1 = STAGE, oV = 2 * STAGE, oT = oV + NX * NX, oQxu = oT + NX * NX,
                        oQuu = oQxu + LDQ * NU + 32, oVx = oQuu + NU * NU, oK = oVx + NX, oX = oK + NU,
-                       oU = oX + NX, oXn = oU + NU, oLam = oXn + NX, WARP = oLam + NX + 2;
+                       oU = oX + NX, oXn = oU + NU, oLam = oXn + NX, oQp = oLam + NX + 2,
+                       oQv = oQp + 8 * NT * LDP, oKm = oQv + 8 * NT, WARP = oKm + NU * LDK + 2;
   static_assert(NX % 2 == 0 && NU % 2 == 0, "16-byte staging needs even block sizes");
   static_assert(N + NU <= 32, "one column per lane");
 };
@@ -328,6 +334,10 @@ __device__ __forceinline__ int small_backward(const Prob& p, double* sw, int lan
   return 0;
 }
 
+}  // namespace mimgpu
+#include "kernels_small_mma.cuh"
+namespace mimgpu {
+
 /* ------------------------------------------------------------------- forward */
 /* SolverSQP::forwardPass + checkKKTConditions + gap norm (src/sqp.cpp:270-305, 244-268,
  * 229-236).  Lane i < NX owns state row i, lane a < NU control row a, lane c < N column c
@@ -462,7 +472,7 @@ __device__ __forceinline__ void small_forward(const Prob& p, double* sw, int lan
 }
 
 /* -------------------------------------------------------------------- kernel */
-template <int NX, int NU, int WPB>
+template <int NX, int NU, int WPB, bool NOMMA = false>
 __global__ void __launch_bounds__(WPB * 32) k_sqp_direction_small(KArgs a, SqpKPar kp) {
   extern __shared__ double smem_small[];
   using C = SmallCfg<NX, NU>;
@@ -474,7 +484,11 @@ __global__ void __launch_bounds__(WPB * 32) k_sqp_direction_small(KArgs a, SqpKP
   Prob p = bind(a, b);
   const double preg = a.preg_arr ? a.preg_arr[b] : kp.preg;
   const double dreg = a.dreg_arr ? a.dreg_arr[b] : kp.dreg;
-  const int st = small_backward<NX, NU>(p, sw, lane, preg, dreg, kp.is_feasible);
+  int st;
+  if constexpr (NX % 4 == 0 && !NOMMA)
+    st = small_backward_mma<NX, NU>(p, sw, lane, preg, dreg, kp.is_feasible);
+  else
+    st = small_backward<NX, NU>(p, sw, lane, preg, dreg, kp.is_feasible);
   if (lane == 0) { a.status[b] = st; a.qp_iters[b] = 0; }
   if (st) {
     cp_async_wait<0>();
