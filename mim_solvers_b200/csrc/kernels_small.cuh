@@ -41,10 +41,14 @@ struct SmallCfg {
   static constexpr int PC0 = 8 * (NX / 8);          /* first published column of Q */
   static constexpr int LDP = 8 * NT - PC0 + 2;      /* leading dim of the published Q block */
   static constexpr int LDK = 24;                    /* leading dim of the shared K (NU x NX) */
-  static constexpr int oS0 = 0, oS1 = STAGE, oV = 2 * STAGE, oT = oV + NX * NX, oQxu = oT + NX * NX,
-                       oQuu = oQxu + LDQ * NU + 32, oVx = oQuu + NU * NU, oK = oVx + NX, oX = oK + NU,
-                       oU = oX + NX, oXn = oU + NU, oLam = oXn + NX, oQp = oLam + NX + 2,
-                       oQv = oQp + 8 * NT * LDP, oKm = oQv + 8 * NT, WARP = oKm + NU * LDK + 2;
+  static constexpr int oS0 = 0, oS1 = STAGE, oV = 2 * STAGE, oT = oV + NX * NX, oVx = oT + NX * NX,
+                       oK = oVx + NX, oX = oK + NU, oU = oX + NX, oXn = oU + NU, oLam = oXn + NX,
+                       oUnion = oLam + NX + 2,
+                       /* DFMA variant: Qxu (+ Qu row), Quu */
+                       oQxu = oUnion, oQuu = oQxu + LDQ * NU + 32, endA = oQuu + NU * NU,
+                       /* DMMA variant: published Q columns, [Qx; Qu], K */
+                       oQp = oUnion, oQv = oQp + 8 * NT * LDP, oKm = oQv + 8 * NT, endB = oKm + NU * LDK + 2,
+                       WARP = ((endA > endB ? endA : endB) + 1) & ~1;
   static_assert(NX % 2 == 0 && NU % 2 == 0, "16-byte staging needs even block sizes");
   static_assert(N + NU <= 32, "one column per lane");
 };
@@ -472,8 +476,14 @@ __device__ __forceinline__ void small_forward(const Prob& p, double* sw, int lan
 }
 
 /* -------------------------------------------------------------------- kernel */
+/* Launch shape per specialisation: warps per CTA and resident CTAs per SM.  The UR5 shape
+ * runs 2 x 7 = 14 problems per SM (register budget 144, 15.7 KB of shared memory per warp):
+ * 148 SMs x 14 = 2072 slots, so a 4096-problem batch is two full waves. */
+template <int NX, int NU> struct SmallTune { static constexpr int WPB = 4, MINB = 1; };
+template <> struct SmallTune<12, 6> { static constexpr int WPB = 2, MINB = 7; };
+
 template <int NX, int NU, int WPB, bool NOMMA = false>
-__global__ void __launch_bounds__(WPB * 32) k_sqp_direction_small(KArgs a, SqpKPar kp) {
+__global__ void __launch_bounds__(WPB * 32, SmallTune<NX, NU>::MINB) k_sqp_direction_small(KArgs a, SqpKPar kp) {
   extern __shared__ double smem_small[];
   using C = SmallCfg<NX, NU>;
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
@@ -505,11 +515,18 @@ __global__ void __launch_bounds__(WPB * 32) k_sqp_direction_small(KArgs a, SqpKP
 }
 
 /* ------------------------------------------------------------------ dispatch */
+/* MIMGPU_SMALL_NOMMA=1 selects the DFMA (CUDA-core) variant of the backward sweep: A/B switch
+ * for profiling, both variants are parity-tested. */
+static inline bool small_nomma() {
+  static const bool v = getenv("MIMGPU_SMALL_NOMMA") != nullptr;
+  return v;
+}
+
 template <int NX, int NU, int WPB>
 static int small_launch_t(const KArgs& a, const SqpKPar& kp, cudaStream_t st, bool configure_only) {
   using C = SmallCfg<NX, NU>;
   const int smem = WPB * C::WARP * (int)sizeof(double);
-  auto kern = k_sqp_direction_small<NX, NU, WPB>;
+  auto kern = small_nomma() ? k_sqp_direction_small<NX, NU, WPB, true> : k_sqp_direction_small<NX, NU, WPB, false>;
   if (configure_only) {
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return 1;
     return 0;
@@ -520,14 +537,13 @@ static int small_launch_t(const KArgs& a, const SqpKPar& kp, cudaStream_t st, bo
 }
 
 #define MIMGPU_SMALL_SHAPES(X) X(12, 6) X(8, 4) X(16, 8) X(4, 2) X(6, 2) X(10, 4)
-constexpr int kSmallWPB = 4;
 
 /* 1 when a specialised SQP kernel exists for this shape (and is configured) */
 static inline int small_kernels_configure(const mimgpu_shape& s) {
   KArgs dummy{};
   SqpKPar kp{};
 #define X(NX_, NU_) \
-  if (s.nx == NX_ && s.nu == NU_) return small_launch_t<NX_, NU_, kSmallWPB>(dummy, kp, nullptr, true) == 0;
+  if (s.nx == NX_ && s.nu == NU_) return small_launch_t<NX_, NU_, SmallTune<NX_, NU_>::WPB>(dummy, kp, nullptr, true) == 0;
   MIMGPU_SMALL_SHAPES(X)
 #undef X
   return 0;
@@ -541,7 +557,7 @@ static inline int small_sqp_direction_launch(const KArgs& a, const SqpKPar& kp, 
                        (uintptr_t)a.Lx | (uintptr_t)a.Lu | (uintptr_t)a.fs | (uintptr_t)a.LxxT;
   if (al & 15) return -1;
 #define X(NX_, NU_) \
-  if (a.sh.nx == NX_ && a.sh.nu == NU_) return small_launch_t<NX_, NU_, kSmallWPB>(a, kp, st, false);
+  if (a.sh.nx == NX_ && a.sh.nu == NU_) return small_launch_t<NX_, NU_, SmallTune<NX_, NU_>::WPB>(a, kp, st, false);
   MIMGPU_SMALL_SHAPES(X)
 #undef X
   return -1;
