@@ -59,10 +59,13 @@ WORKLOADS = {
 }
 
 
+QP_ITERS = 50  # --qp-iters (experiments only; the reported protocol is 50)
+
+
 def csqp_bench_params():
     """benchmarks/solo12.cpp:213-216: eps_abs = eps_rel = 0, max_qp_iters = 50, no
     equality-QP initial guess -> exactly 50 ADMM iterations per QP."""
-    return _capi.default_csqp_params(eps_abs=0.0, eps_rel=0.0, max_qp_iters=50,
+    return _capi.default_csqp_params(eps_abs=0.0, eps_rel=0.0, max_qp_iters=QP_ITERS,
                                      equality_qp_initial_guess=0)
 
 
@@ -258,7 +261,7 @@ def gpu_arm(args, rank, world, local_rank):
         hbm_peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
     kernel_ms = float(np.mean(per))
     bytes_qp = batch.algorithmic_bytes_per_qp()
-    flops_qp = batch.flops_csqp_qp(50, False) if solver == "csqp" else batch.flops_sqp_qp()
+    flops_qp = batch.flops_csqp_qp(QP_ITERS, False) if solver == "csqp" else batch.flops_sqp_qp()
     ach_gbs = bytes_qp * B / (kernel_ms * 1e-3) / 1e9
     roof = {"bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": ach_gbs / hbm_peak,
             "traffic": None, "peak_source": peak_src, "kernel_ms": kernel_ms,
@@ -339,7 +342,7 @@ def gpu_arm(args, rank, world, local_rank):
                    "distinct_problems_per_gpu": min(B, args.distinct),
                    "l2": f"inputs {batch.nbytes() / 1e6:.0f} MB per step > 126 MB L2 (no flush needed)"
                          if batch.nbytes() > 2 * 126e6 else "inputs smaller than 2x L2",
-                   "csqp_protocol": "eps_abs=eps_rel=0, 50 ADMM iterations, no eq. guess" if solver == "csqp" else None},
+                   "csqp_protocol": f"eps_abs=eps_rel=0, {QP_ITERS} ADMM iterations, no eq. guess" if solver == "csqp" else None},
         "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
         "clocks": clk.summary(),
         "batch_summary": {"max_kkt": float(red[0]), "sum_qp_iters": int(red[1]), "n_converged": int(red[2]),
@@ -360,7 +363,10 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--qp-iters", type=int, default=50, help="ADMM iterations per CSQP QP (protocol: 50)")
     args = ap.parse_args()
+    global QP_ITERS
+    QP_ITERS = args.qp_iters
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

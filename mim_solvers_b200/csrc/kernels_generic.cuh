@@ -235,6 +235,7 @@ enum { MODE_DDP = 0, MODE_EQ = 1, MODE_FULL = 2 };
 struct RicPar {
   double preg, dreg, sigma;
   int is_feasible;
+  int dbg = 0; /* debug checkpoints of kernels_ric.cuh (0 = off) */
 };
 
 /* MODE_DDP : SolverDDP::backwardPass (src/ddp.cpp:265-348) -- SQP and FDDP.

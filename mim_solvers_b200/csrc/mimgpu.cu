@@ -17,6 +17,7 @@
 
 #include "kernels_generic.cuh"
 #include "kernels_small.cuh"
+#include "kernels_cta.cuh"
 
 using namespace mimgpu;
 
@@ -53,6 +54,8 @@ struct mimgpu_ctx {
   int smem_bytes = 0;
   int sm_count = 148;
   int use_small = 0;               /* specialised small-shape kernel available */
+  CtaPlan cplan{};                 /* DMMA CTA-per-problem SQP / FDDP kernel (kernels_cta.cuh) */
+  StreamPlan splan{};              /* streaming CSQP kernel (kernels_stream.cuh), ok = 0: not available */
 };
 
 static size_t deriv_sizes(const mimgpu_shape& s, size_t n[20]) {
@@ -222,6 +225,8 @@ static int configure_launch(mimgpu_ctx* c) {
   CU(cudaFuncSetAttribute(k_fddp_direction_generic, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
   CU(cudaFuncSetAttribute(k_csqp_direction_generic, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
   c->use_small = small_kernels_configure(s);
+  c->splan = stream_plan(s, stage, max_smem);
+  c->cplan = cta_plan(s, stage, max_smem);
   return MIMGPU_OK;
 }
 
@@ -410,6 +415,9 @@ int mimgpu_sqp_direction(mimgpu_ctx* c, const mimgpu_sqp_params* p, void* stream
     if (rc == 0) return post_launch(c, "k_sqp_direction_small");
     if (rc > 0) return fail(MIMGPU_ERR_CUDA, "small kernel launch configuration failed");
   }
+  if (c->cplan.ok && !c->use_small && getenv("MIMGPU_FORCE_GENERIC") == nullptr &&
+      (((uintptr_t)c->k.Fx | (uintptr_t)c->k.Fu) & 15) == 0 && cta_sqp_launch(c->k, kp, false, c->cplan, st) == 0)
+    return post_launch(c, "k_sqp_direction_cta");
   k_sqp_direction_generic<<<c->k.n_active, c->nt, c->smem_bytes, st>>>(c->k, kp);
   return post_launch(c, "k_sqp_direction_generic");
 }
@@ -420,6 +428,10 @@ int mimgpu_fddp_direction(mimgpu_ctx* c, const mimgpu_sqp_params* p, void* strea
   if (!p) return fail(MIMGPU_ERR_INVALID, "null params");
   if (c->k.n_active == 0) return MIMGPU_OK;
   SqpKPar kp{p->preg, p->dreg, p->mu_dynamic, p->is_feasible};
+  if (c->cplan.ok && getenv("MIMGPU_FORCE_GENERIC") == nullptr &&
+      (((uintptr_t)c->k.Fx | (uintptr_t)c->k.Fu) & 15) == 0 &&
+      cta_sqp_launch(c->k, kp, true, c->cplan, (cudaStream_t)stream) == 0)
+    return post_launch(c, "k_fddp_direction_cta");
   k_fddp_direction_generic<<<c->k.n_active, c->nt, c->smem_bytes, (cudaStream_t)stream>>>(c->k, kp);
   return post_launch(c, "k_fddp_direction_generic");
 }
@@ -450,6 +462,12 @@ int mimgpu_csqp_direction(mimgpu_ctx* c, const mimgpu_csqp_params* p, int with_k
   CsqpKPar kp;
   kp.q = *p;
   kp.with_kkt = with_kkt;
+  if (c->splan.ok && getenv("MIMGPU_FORCE_GENERIC") == nullptr) {
+    /* TMA bulk copies need 16-byte aligned sources (block sizes are even by construction) */
+    const uintptr_t al = (uintptr_t)c->k.Fx | (uintptr_t)c->k.Fu | (uintptr_t)c->k.Gx | (uintptr_t)c->k.Gu;
+    if ((al & 15) == 0 && stream_csqp_launch(c->k, *p, with_kkt, c->splan, (cudaStream_t)stream) == 0)
+      return post_launch(c, "k_csqp_direction_stream");
+  }
   k_csqp_direction_generic<<<c->k.n_active, c->nt, c->smem_bytes, (cudaStream_t)stream>>>(c->k, kp);
   return post_launch(c, "k_csqp_direction_generic");
 }
