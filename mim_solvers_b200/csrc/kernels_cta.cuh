@@ -199,7 +199,7 @@ static inline int stream_csqp_launch(const KArgs& a, const mimgpu_csqp_params& q
 
 /* ============================================================ SQP / FDDP CTA kernels */
 struct CtaPlan {
-  int ok, nt, smem_bytes, nbuf;
+  int ok, nt, smem_bytes, nbuf, ns;
 };
 
 __device__ __noinline__ void sqp_forward_kkt_ool(const Prob& p, double* sm, const Smem& s, double mu, int stage_fx) {
@@ -212,20 +212,24 @@ __device__ __noinline__ void fddp_expected_improvement_ool(const Prob& p, double
 /* SolverSQP::computeDirection (src/sqp.cpp:224-242) / SolverFDDP::computeDirection +
  * updateExpectedImprovement (src/fddp.cpp:189-204, 256-279): DMMA backward sweep, then the
  * shape-generic forward pass / KKT (SQP) or expected-improvement reductions (FDDP). */
+template <int NX, int NU>
+struct CtaTune { /* 4 lanes per right-hand side of the gain solve */
+  static constexpr int MAXT = ((4 * (NX + 1) + 31) / 32) * 32 > 512 ? 512 : ((4 * (NX + 1) + 31) / 32) * 32;
+};
+
 template <int NX, int NU, bool FDDP>
-__global__ void __launch_bounds__(256, 1) k_sqp_direction_cta(KArgs a, SqpKPar kp, int nbuf) {
+__global__ void __launch_bounds__(CtaTune<NX, NU>::MAXT, 1) k_sqp_direction_cta(KArgs a, SqpKPar kp, int nbuf, int ns) {
   extern __shared__ __align__(16) double sm_cta[];
   if ((int)blockIdx.x >= a.n_active) return;
   const int b = a.active ? a.active[blockIdx.x] : (int)blockIdx.x;
   Prob p = bind(a, b);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sm_cta);
-  double* um = sm_cta + 4;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sm_cta); /* [0,1]: backward sweep, [2..5): forward pipeline */
+  double* um = sm_cta + 8;
   const RicSmem rs = ric_layout<NX, NU>(0, 0, false, nbuf);
   const Smem gs = smem_layout(NX, NU, 0, 0, a.stage_fx);
   uint32_t seq = 0u;
   if (threadIdx.x == 0) {
-    mbar_init(bars, 1);
-    mbar_init(bars + 1, 1);
+    for (int i = 0; i < 5; ++i) mbar_init(bars + i, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
@@ -251,8 +255,19 @@ __global__ void __launch_bounds__(256, 1) k_sqp_direction_cta(KArgs a, SqpKPar k
     return;
   }
   __syncthreads();
-  if (FDDP) fddp_expected_improvement_ool(p, um, gs, kp.is_feasible);
-  else sqp_forward_kkt_ool(p, um, gs, kp.mu_dynamic, a.stage_fx);
+  if (FDDP) {
+    fddp_expected_improvement_ool(p, um, gs, kp.is_feasible);
+  } else if (ns >= 2) {
+    fence_proxy_async(); /* K, Vxx written through the generic proxy, read back by TMA */
+    __syncthreads();
+    PipeSqp<NX, NU> pipe;
+    pipe.bars = bars + 2;
+    pipe.stages = um + SqpFwdSmem<NX, NU>::stages;
+    pipe.ns = ns; pipe.n_issue = 0; pipe.n_wait = 0;
+    stream_sqp_forward<NX, NU, 4>(p, um, pipe, kp.mu_dynamic);
+  } else {
+    sqp_forward_kkt_ool(p, um, gs, kp.mu_dynamic, a.stage_fx);
+  }
 }
 
 #define MIMGPU_CTA_SHAPES(X) X(36, 12) X(64, 32) X(76, 32) X(32, 16) X(16, 8) X(24, 12) X(48, 24)
@@ -261,15 +276,18 @@ template <int NX, int NU>
 static CtaPlan cta_plan_t(const mimgpu_shape& sh, int stage_fx, int max_smem) {
   CtaPlan pl{};
   const Smem gs = smem_layout(NX, NU, 0, 0, stage_fx);
-  int nt = 32 * RicCfg<NX, NU>::NT;
-  if (nt < 4 * (NX + NU)) nt = ((4 * (NX + NU) + 31) / 32) * 32;
-  if (nt > 256) nt = 256;
-  pl.nt = nt;
+  pl.nt = CtaTune<NX, NU>::MAXT;
   for (int nbuf = 2; nbuf >= 1; --nbuf) {
     const RicSmem rs = ric_layout<NX, NU>(0, 0, false, nbuf);
-    const int tot = 4 + (rs.total > gs.total ? rs.total : gs.total);
-    if (tot * 8 > max_smem) continue;
-    pl.nbuf = nbuf; pl.smem_bytes = tot * 8;
+    int tot = rs.total > gs.total ? rs.total : gs.total;
+    if ((8 + tot) * 8 > max_smem) continue;
+    /* streaming forward pass: 3 or 2 stages next to its vectors, inside the same union */
+    pl.ns = 0;
+    for (int ns = 3; ns >= 2; --ns) {
+      const int f = SqpFwdSmem<NX, NU>::stages + ns * PipeSqp<NX, NU>::STAGE;
+      if ((8 + f) * 8 <= max_smem) { pl.ns = ns; if (f > tot) tot = f; break; }
+    }
+    pl.nbuf = nbuf; pl.smem_bytes = (8 + tot) * 8;
     if (cudaFuncSetAttribute(k_sqp_direction_cta<NX, NU, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              pl.smem_bytes) != cudaSuccess ||
         cudaFuncSetAttribute(k_sqp_direction_cta<NX, NU, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -292,8 +310,8 @@ static inline CtaPlan cta_plan(const mimgpu_shape& sh, int stage_fx, int max_sme
 static inline int cta_sqp_launch(const KArgs& a, const SqpKPar& kp, bool fddp, const CtaPlan& pl, cudaStream_t st) {
 #define X(NX_, NU_)                                                                                      \
   if (a.sh.nx == NX_ && a.sh.nu == NU_) {                                                                \
-    if (fddp) k_sqp_direction_cta<NX_, NU_, true><<<a.n_active, pl.nt, pl.smem_bytes, st>>>(a, kp, pl.nbuf);  \
-    else k_sqp_direction_cta<NX_, NU_, false><<<a.n_active, pl.nt, pl.smem_bytes, st>>>(a, kp, pl.nbuf);      \
+    if (fddp) k_sqp_direction_cta<NX_, NU_, true><<<a.n_active, pl.nt, pl.smem_bytes, st>>>(a, kp, pl.nbuf, pl.ns);  \
+    else k_sqp_direction_cta<NX_, NU_, false><<<a.n_active, pl.nt, pl.smem_bytes, st>>>(a, kp, pl.nbuf, pl.ns);      \
     return 0;                                                                                            \
   }
   MIMGPU_CTA_SHAPES(X)

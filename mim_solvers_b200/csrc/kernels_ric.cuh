@@ -422,26 +422,57 @@ __device__ __noinline__ int ric_backward_mma(const Prob& p, double* sm, const Ri
       else drain(t);
       return MIMGPU_STATUS_LLT | (t << 8);
     }
-    for (int c = tid; c < NX + 1; c += nth) {
-      double x[NU];
-      if (c < NX) {
+    /* K = Quu^-1 Qxu^T (nx right-hand sides) and k = Quu^-1 Qu: QS lanes share one right-hand
+     * side, lane q owns rows i = q (mod QS); per elimination step the owner of row j scales it
+     * and broadcasts it by shuffle, every lane updates its own rows (independent FMAs).  Each
+     * x[i] still subtracts its terms in the reference's order (j ascending / descending). */
+    {
+      constexpr int QS = 4, RL = (NU + QS - 1) / QS; /* rows per lane */
+      const int qs = tid & (QS - 1), ngq = nth / QS;
+      for (int c0 = 0; c0 < NX + 1; c0 += ngq) {
+        const int c = c0 + tid / QS;
+        const bool valid = c < NX + 1;
+        double x[RL];
 #pragma unroll
-        for (int a = 0; a < NU; ++a) x[a] = sQxu[c + NX * a]; /* K = Qxu^T */
-      } else {
+        for (int r = 0; r < RL; ++r) {
+          const int i = r * QS + qs;
+          x[r] = (valid && i < NU) ? ((c < NX) ? sQxu[c + NX * i] : sQv[NX + i]) : 0.0;
+        }
 #pragma unroll
-        for (int a = 0; a < NU; ++a) x[a] = sQv[NX + a];
-      }
-      llt_solve_regs<NU>(sL, linv, x);
-      if (c < NX) {
+        for (int j = 0; j < NU; ++j) { /* L y = b */
+          const double xj = __shfl_sync(0xffffffffu, x[j / QS] * linv[j], (lane & ~(QS - 1)) | (j % QS));
+          if (qs == j % QS) x[j / QS] = xj;
 #pragma unroll
-        for (int a = 0; a < NU; ++a) { sK[a * NX + c] = x[a]; p.K[(size_t)t * NX * NU + a * NX + c] = x[a]; }
-      } else {
+          for (int r = j / QS; r < RL; ++r) {
+            const int i = r * QS + qs;
+            if (i > j && i < NU) x[r] = fma(-sL[i + NU * j], xj, x[r]);
+          }
+        }
 #pragma unroll
-        for (int a = 0; a < NU; ++a) { skff[a] = x[a]; p.kff[(size_t)t * NU + a] = x[a]; }
+        for (int j = NU - 1; j >= 0; --j) { /* L^T x = y */
+          const double xj = __shfl_sync(0xffffffffu, x[j / QS] * linv[j], (lane & ~(QS - 1)) | (j % QS));
+          if (qs == j % QS) x[j / QS] = xj;
+#pragma unroll
+          for (int r = 0; r <= j / QS; ++r) {
+            const int i = r * QS + qs;
+            if (i < j) x[r] = fma(-sL[j + NU * i], xj, x[r]);
+          }
+        }
+        if (valid) {
+#pragma unroll
+          for (int r = 0; r < RL; ++r) {
+            const int i = r * QS + qs;
+            if (i < NU) {
+              if (c < NX) sK[i * NX + c] = x[r];
+              else { skff[i] = x[r]; p.kff[(size_t)t * NU + i] = x[r]; }
+            }
+          }
+        }
       }
     }
     for (int e = tid; e < NU * NU; e += nth) p.L[(size_t)t * NU * NU + e] = sL[e];
     __syncthreads(); /* S5: K, k complete */
+    for (int e = tid; e < NU * NX; e += nth) p.K[(size_t)t * NX * NU + e] = sK[e];
     /* ---- step F: M = Qxx - Qxu K on the upper tiles; Vx = Qx - K^T Qu; Quuk */
     {
       int idx = 0;

@@ -518,4 +518,210 @@ __device__ __noinline__ void stream_forward_update(const Prob& p, double* sm, co
   __syncthreads();
 }
 
+/* ------------------------------------------------------------ SQP forward pass */
+/* stage of knot t: [Fx][Fu][K][Vxx_{t+1}] */
+template <int NX, int NU>
+struct PipeSqp {
+  uint64_t* bars;
+  double* stages;
+  int ns;
+  uint32_t n_issue, n_wait;
+  static constexpr int STAGE = 2 * NX * NX + 2 * NX * NU;
+  __device__ __forceinline__ void issue(const Prob& p, int t) {
+    const int slot = n_issue % ns;
+    if (threadIdx.x == 0) {
+      double* dst = stages + (size_t)slot * STAGE;
+      uint64_t* bar = bars + slot;
+      mbar_expect_tx(bar, (uint32_t)STAGE * 8u);
+      tma_bulk_g2s(dst, p.Fx + (size_t)t * NX * NX, NX * NX * 8, bar);
+      tma_bulk_g2s(dst + NX * NX, p.Fu + (size_t)t * NX * NU, NX * NU * 8, bar);
+      tma_bulk_g2s(dst + NX * NX + NX * NU, p.K + (size_t)t * NX * NU, NX * NU * 8, bar);
+      tma_bulk_g2s(dst + NX * NX + 2 * NX * NU, p.Vxx + (size_t)(t + 1) * NX * NX, NX * NX * 8, bar);
+    }
+    ++n_issue;
+  }
+  __device__ __forceinline__ const double* acquire() {
+    const int slot = n_wait % ns;
+    mbar_wait(bars + slot, (n_wait / ns) & 1u);
+    ++n_wait;
+    return stages + (size_t)slot * STAGE;
+  }
+};
+
+/* shared memory (doubles) of stream_sqp_forward next to the stages */
+template <int NX, int NU>
+struct SqpFwdSmem {
+  static constexpr int NV = 3 * NX + 2 * NU;
+  static constexpr int vec0 = 0, vec1 = NV, x0 = 2 * NV, x1 = x0 + NX, u = x1 + NX, dm = u + NU, lam0 = dm + NX,
+                       lam1 = lam0 + NX, red = lam1 + NX, stages = red + 64;
+};
+
+/* SolverSQP::forwardPass (src/sqp.cpp:270-305) fused with checkKKTConditions
+ * (src/sqp.cpp:244-268) and the gap norm / merit of computeDirection (src/sqp.cpp:229-236):
+ * the knot's Fx, Fu, K, Vxx+ are streamed by TMA NS knots ahead, vectors through registers. */
+template <int NX, int NU, int SPLIT>
+__device__ __noinline__ void stream_sqp_forward(const Prob& p, double* sm, PipeSqp<NX, NU>& pipe, double mu_dynamic) {
+  using S = SqpFwdSmem<NX, NU>;
+  constexpr int N = NX + NU, VPT = 3;
+  const int T = p.T, tid = threadIdx.x, nth = blockDim.x, lane = tid & 31;
+  double *su = sm + S::u, *sdm = sm + S::dm, *red = sm + S::red;
+  /* pack of knot t: [k NU][fs_{t+1} NX][Vx_{t+1} NX][Lx NX][Lu NU] */
+  constexpr int oK = 0, oFs = NU, oVx = NU + NX, oLx = NU + 2 * NX, nv = S::NV;
+  VecSrc vs[VPT];
+  double vr[VPT];
+#pragma unroll
+  for (int j = 0; j < VPT; ++j) {
+    const int e = tid + j * nth;
+    vs[j].base = nullptr; vs[j].stride = 0;
+    if (e < oFs) { vs[j].base = p.kff + e; vs[j].stride = NU; }
+    else if (e < oVx) { vs[j].base = p.fs + NX + (e - oFs); vs[j].stride = NX; }
+    else if (e < oLx) { vs[j].base = p.Vx + NX + (e - oVx); vs[j].stride = NX; }
+    else if (e < oLx + NX) { vs[j].base = p.Lx + (e - oLx); vs[j].stride = NX; }
+    else if (e < nv) { vs[j].base = p.Lu + (e - oLx - NX); vs[j].stride = NU; }
+  }
+  __syncthreads();
+  for (int j = 0; j < pipe.ns - 1; ++j)
+    if (j < T) pipe.issue(p, j);
+#pragma unroll
+  for (int j = 0; j < VPT; ++j) {
+    const int e = tid + j * nth;
+    if (vs[j].base) (sm + S::vec0)[e] = vs[j].base[0];
+    vr[j] = (vs[j].base && T >= 2) ? vs[j].base[(size_t)vs[j].stride] : 0.0;
+  }
+  double xg = 0.0, ug = 0.0, gap = 0.0, kkt = 0.0;
+  /* knot 0: dx_0 is whatever the member holds (0); lag_mul_0 = Vxx_0 (dx_0 - fs_0) + Vx_0 */
+  for (int i = tid; i < NX; i += nth) {
+    const double x0 = p.dx[i], f0 = p.fs[i];
+    (sm + S::x0)[i] = x0;
+    sdm[i] = x0 - f0;
+    xg += fabs(x0); gap += fabs(f0); kkt = nmax(kkt, fabs(f0));
+  }
+  __syncthreads();
+  for (int i = tid; i < NX; i += nth) {
+    double acc = 0.0;
+    for (int j = 0; j < NX; ++j) acc += p.Vxx[i + NX * j] * sdm[j];
+    const double v = acc + p.Vx[i];
+    (sm + S::lam0)[i] = v;
+    p.lag[i] = v;
+  }
+  __syncthreads();
+  const int grp = tid / SPLIT, q = tid % SPLIT, ngrp = nth / SPLIT;
+  const int h = lane >> 4, l16 = lane & 15, w16 = (tid >> 5) * 16, n16 = (nth >> 5) * 16;
+  for (int t = 0; t < T; ++t) {
+    const double* st = pipe.acquire();
+    const double *sFx = st, *sFu = st + NX * NX, *sK = st + NX * NX + NX * NU, *sV = sK + NX * NU;
+    const double* x = sm + ((t & 1) ? S::x1 : S::x0);
+    double* xn = sm + ((t & 1) ? S::x0 : S::x1);
+    const double* lam = sm + ((t & 1) ? S::lam1 : S::lam0);
+    double* lamn = sm + ((t & 1) ? S::lam0 : S::lam1);
+    const double* v = sm + ((t & 1) ? S::vec1 : S::vec0);
+    /* F1: du = -K dx - k  (src/sqp.cpp:285-286) */
+    for (int o0 = 0; o0 < NU; o0 += ngrp) {
+      const int a = o0 + grp;
+      const bool valid = a < NU;
+      const double* Kr = sK + NX * (valid ? a : 0);
+      double acc = 0.0;
+#pragma unroll
+      for (int k = 0; k < (NX + SPLIT - 1) / SPLIT; ++k) {
+        const int kk = k * SPLIT + q;
+        if (kk < NX) acc = fma(Kr[kk], x[kk], acc);
+      }
+      acc = split_reduce<SPLIT>(acc);
+      if (valid && q == 0) {
+        double u = -acc;
+        u -= v[oK + a];
+        su[a] = u;
+        p.du[(size_t)t * NU + a] = u;
+        ug += fabs(u);
+      }
+    }
+    __syncthreads(); /* 1: du visible; knot t-1 completely consumed */
+    if (t + pipe.ns - 1 < T) pipe.issue(p, t + pipe.ns - 1);
+    if (t + 1 < T) {
+      double* vn = sm + ((t & 1) ? S::vec0 : S::vec1);
+#pragma unroll
+      for (int j = 0; j < VPT; ++j) {
+        const int e = tid + j * nth;
+        if (vs[j].base) vn[e] = vr[j];
+      }
+      if (t + 2 < T) {
+#pragma unroll
+        for (int j = 0; j < VPT; ++j)
+          if (vs[j].base) vr[j] = vs[j].base[(size_t)(t + 2) * vs[j].stride];
+      }
+    }
+    /* F2: dx+ = fs+ + Fu du + Fx dx  (src/sqp.cpp:287-289); two half-warps share a row */
+    for (int o0 = 0; o0 < NX; o0 += n16) {
+      const int i = o0 + w16 + l16;
+      const int ic = i < NX ? i : 0;
+      double a1 = 0.0, a2 = 0.0;
+#pragma unroll
+      for (int a = 0; a < NU / 2; ++a) a2 = fma(sFu[ic + NX * (2 * a + h)], su[2 * a + h], a2);
+#pragma unroll
+      for (int j = 0; j < NX / 2; ++j) a1 = fma(sFx[ic + NX * (2 * j + h)], x[2 * j + h], a1);
+      a1 += __shfl_xor_sync(0xffffffffu, a1, 16);
+      a2 += __shfl_xor_sync(0xffffffffu, a2, 16);
+      if (i < NX && h == 0) {
+        const double fsn = v[oFs + i];
+        double xv = fsn;
+        xv += a2;
+        xv += a1;
+        xn[i] = xv;
+        sdm[i] = xv - fsn;
+        p.dx[(size_t)(t + 1) * NX + i] = xv;
+        xg += fabs(xv); gap += fabs(fsn); kkt = nmax(kkt, fabs(fsn));
+      }
+    }
+    __syncthreads(); /* 2: dx+ - fs+ visible */
+    /* F3: lag_mul+ = Vxx+ (dx+ - fs+) + Vx+  (src/sqp.cpp:282-284, 296-298) */
+    for (int o0 = 0; o0 < NX; o0 += n16) {
+      const int i = o0 + w16 + l16;
+      const int ic = i < NX ? i : 0;
+      double a1 = 0.0;
+#pragma unroll
+      for (int j = 0; j < NX / 2; ++j) a1 = fma(sV[ic + NX * (2 * j + h)], sdm[2 * j + h], a1);
+      a1 += __shfl_xor_sync(0xffffffffu, a1, 16);
+      if (i < NX && h == 0) {
+        const double lv = a1 + v[oVx + i];
+        lamn[i] = lv;
+        p.lag[(size_t)(t + 1) * NX + i] = lv;
+      }
+    }
+    __syncthreads(); /* 3: lag_mul+ visible */
+    /* F4: stationarity rows of knot t  (src/sqp.cpp:249-258) */
+    for (int o0 = 0; o0 < N; o0 += ngrp) {
+      const int o = o0 + grp;
+      const bool valid = o < N;
+      const double* Fc = sFx + NX * (valid ? o : 0); /* [Fx Fu] are adjacent in the stage */
+      double acc = 0.0;
+#pragma unroll
+      for (int k = 0; k < (NX + SPLIT - 1) / SPLIT; ++k) {
+        const int kk = k * SPLIT + q;
+        if (kk < NX) acc = fma(Fc[kk], lamn[kk], acc);
+      }
+      acc = split_reduce<SPLIT>(acc);
+      if (valid && q == 0) {
+        double r = v[oLx + o] + acc; /* [Lx; Lu] are adjacent in the pack */
+        if (o < NX) r -= lam[o];
+        kkt = nmax(kkt, fabs(r));
+      }
+    }
+  }
+  __syncthreads();
+  {
+    const double* lam = sm + ((T & 1) ? S::lam1 : S::lam0);
+    for (int i = tid; i < NX; i += nth) kkt = nmax(kkt, fabs(p.LxT[i] - lam[i])); /* src/sqp.cpp:259-262 */
+  }
+  kkt = cta_max(kkt, red);
+  xg = cta_sum(xg, red); ug = cta_sum(ug, red); gap = cta_sum(gap, red);
+  if (tid == 0) {
+    const size_t B = p.B, b = p.b;
+    p.scal[MIMGPU_S_KKT * B + b] = kkt;
+    p.scal[MIMGPU_S_GAP_NORM * B + b] = gap;
+    p.scal[MIMGPU_S_MERIT * B + b] = p.cost + mu_dynamic * gap;
+    p.scal[MIMGPU_S_XGRAD_NORM * B + b] = xg / (double)(T + 1);
+    p.scal[MIMGPU_S_UGRAD_NORM * B + b] = ug / (double)T;
+  }
+}
+
 }  // namespace mimgpu
