@@ -37,6 +37,7 @@ sys.path.insert(0, str(ROOT))
 
 from mim_solvers_b200 import _capi  # noqa: E402
 from mim_solvers_b200.problems import CONFIGS, OCPBatch, make_config, tile_batch  # noqa: E402
+from mim_solvers_b200.sharding import allreduce_max, allreduce_summary  # noqa: E402
 
 METRIC = "OCP QP solves/sec (batched FP64 Riccati+ADMM)"
 UNIT = "QP/s"
@@ -239,17 +240,10 @@ def gpu_arm(args, rank, world, local_rank):
     launches = eng.launch_count - l0
     per = [evs[i].elapsed_time(evs[i + 1]) for i in range(args.steps)]
     total_ms = evs[0].elapsed_time(evs[-1])
-    summ = eng.summary(1e-6)
-    tt = torch.tensor([total_ms], dtype=torch.float64, device=dev)
-    red = torch.tensor([summ["max_kkt"], float(summ["sum_qp_iters"]), float(summ["n_converged"]),
-                        float(summ["n_failed"])], dtype=torch.float64, device=dev)
-    if world > 1:  # the only collectives -- max time, batch-wide summary
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        mk = red[:1].clone()
-        dist.all_reduce(mk, op=dist.ReduceOp.MAX)
-        dist.all_reduce(red, op=dist.ReduceOp.SUM)
-        red[0] = mk[0]
-    total_ms = float(tt.item())
+    # the only collectives -- max time over ranks, batch-wide summary
+    summ = allreduce_summary(eng.summary(1e-6), device=dev)
+    total_ms = allreduce_max(total_ms, device=dev)
+    red = [summ["max_kkt"], summ["sum_qp_iters"], summ["n_converged"], summ["n_failed"]]
     ms_per_step = total_ms / args.steps
     value = world * B / (ms_per_step * 1e-3)
 
@@ -316,12 +310,9 @@ def gpu_arm(args, rank, world, local_rank):
         for _ in range(n_e2e):
             e2e_step()
         barrier()
-        dt = torch.tensor([(time.perf_counter() - t0) / n_e2e], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
-        launches_e2e = eng2.launch_count
-        e2e = {"value": world * B / float(dt.item()), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
-               "d2h_bytes_per_step": int(d2h), "ms_per_step": float(dt.item()) * 1e3, "steps": n_e2e,
+        dt = allreduce_max((time.perf_counter() - t0) / n_e2e, device=dev)
+        e2e = {"value": world * B / dt, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+               "d2h_bytes_per_step": int(d2h), "ms_per_step": dt * 1e3, "steps": n_e2e,
                "max_kkt": float(kkt.max())}
         del keep
 

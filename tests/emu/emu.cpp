@@ -24,13 +24,13 @@ static std::vector<double> smem_for(const KArgs* a) {
 int emu_sqp_direction(const KArgs* a, const mimgpu_sqp_params* p) {
   std::vector<double> sm = smem_for(a);
   SqpKPar kp{p->preg, p->dreg, p->mu_dynamic, p->is_feasible};
-  for (int b = 0; b < a->sh.B; ++b) sqp_direction_body(*a, b, sm.data(), kp);
+  for (int i_ = 0, b = 0; i_ < a->n_active && ((b = a->active ? a->active[i_] : i_), true); ++i_) sqp_direction_body(*a, b, sm.data(), kp);
   return 0;
 }
 int emu_fddp_direction(const KArgs* a, const mimgpu_sqp_params* p) {
   std::vector<double> sm = smem_for(a);
   SqpKPar kp{p->preg, p->dreg, p->mu_dynamic, p->is_feasible};
-  for (int b = 0; b < a->sh.B; ++b) fddp_direction_body(*a, b, sm.data(), kp);
+  for (int i_ = 0, b = 0; i_ < a->n_active && ((b = a->active ? a->active[i_] : i_), true); ++i_) fddp_direction_body(*a, b, sm.data(), kp);
   return 0;
 }
 int emu_csqp_direction(const KArgs* a, const mimgpu_csqp_params* p, int with_kkt) {
@@ -38,16 +38,16 @@ int emu_csqp_direction(const KArgs* a, const mimgpu_csqp_params* p, int with_kkt
   CsqpKPar kp;
   kp.q = *p;
   kp.with_kkt = with_kkt;
-  for (int b = 0; b < a->sh.B; ++b) csqp_direction_body(*a, b, sm.data(), kp);
+  for (int i_ = 0, b = 0; i_ < a->n_active && ((b = a->active ? a->active[i_] : i_), true); ++i_) csqp_direction_body(*a, b, sm.data(), kp);
   return 0;
 }
 int emu_csqp_reset_rho(const KArgs* a, const mimgpu_csqp_params* p) {
-  for (int b = 0; b < a->sh.B; ++b) csqp_reset_rho_body(*a, b, p->rho_sparse_base, p->rho_min);
+  for (int i_ = 0, b = 0; i_ < a->n_active && ((b = a->active ? a->active[i_] : i_), true); ++i_) csqp_reset_rho_body(*a, b, p->rho_sparse_base, p->rho_min);
   return 0;
 }
 int emu_csqp_calc_norms(const KArgs* a) {
   double red[64];
-  for (int b = 0; b < a->sh.B; ++b) csqp_calc_norms_body(*a, b, red);
+  for (int i_ = 0, b = 0; i_ < a->n_active && ((b = a->active ? a->active[i_] : i_), true); ++i_) csqp_calc_norms_body(*a, b, red);
   return 0;
 }
 }

@@ -86,10 +86,29 @@ class EmuEngine:
         self._k = k
 
     def field(self, name):
-        return self._f[name]
+        return self._f[name].copy()
+
+    def upload(self, batch):
+        self.batch = batch
+        for n in _capi.DERIV_FIELDS:
+            a = batch.arrays[n]
+            setattr(self._k, _DERIV_MAP.get(n, n), a.ctypes.data if a.size else None)
+
+    def set_reg(self, preg=None, dreg=None):
+        self._preg = None if preg is None else np.ascontiguousarray(preg, dtype=np.float64).copy()
+        self._dreg = None if dreg is None else np.ascontiguousarray(dreg, dtype=np.float64).copy()
+        self._k.preg_arr = None if preg is None else self._preg.ctypes.data
+        self._k.dreg_arr = None if dreg is None else self._dreg.ctypes.data
+
+    def set_active(self, idx=None):
+        if idx is None:
+            self._k.active, self._k.n_active = None, self._shape.B
+            return
+        self._active = np.ascontiguousarray(idx, dtype=np.int32).copy()
+        self._k.active, self._k.n_active = self._active.ctypes.data, len(self._active)
 
     def scalar(self, name):
-        return self._scal[_capi.SCALARS[name]]
+        return self._scal[_capi.SCALARS[name]].copy()
 
     def sqp_direction(self, params=None, with_kkt=True):
         p = params or _capi.default_sqp_params()
