@@ -8,6 +8,7 @@
  *   k_fddp_direction_cta     SolverFDDP::computeDirection (src/fddp.cpp:189-204)
  */
 #pragma once
+#include "launchers.h"
 #include "kernels_ric.cuh"
 #include "kernels_stream.cuh"
 
@@ -17,12 +18,12 @@ namespace mimgpu {
 /* out-of-line copies of the shape-generic pieces: keeps the register allocation of the
  * streaming sweeps independent of the (much larger) full Riccati sweep */
 template <int MODE>
-__device__ __noinline__ int riccati_backward_ool(const Prob& p, double* sm, const Smem& s, const RicPar& rp,
+static __device__ __noinline__ int riccati_backward_ool(const Prob& p, double* sm, const Smem& s, const RicPar& rp,
                                                  int stage_fx) {
   return riccati_backward<MODE>(p, sm, s, rp, stage_fx);
 }
-__device__ __noinline__ void csqp_forward_eq_ool(const Prob& p, double* sm, const Smem& s) { csqp_forward_eq(p, sm, s); }
-__device__ __noinline__ void csqp_kkt_ool(const Prob& p, double* sm, const Smem& s) { csqp_kkt(p, sm, s); }
+static __device__ __noinline__ void csqp_forward_eq_ool(const Prob& p, double* sm, const Smem& s) { csqp_forward_eq(p, sm, s); }
+static __device__ __noinline__ void csqp_kkt_ool(const Prob& p, double* sm, const Smem& s) { csqp_kkt(p, sm, s); }
 
 struct StreamKPar {
   mimgpu_csqp_params q;
@@ -136,9 +137,6 @@ k_csqp_direction_stream(KArgs a, StreamKPar kp) {
 /* ------------------------------------------------------------------- dispatch */
 #define MIMGPU_STREAM_SHAPES(X) X(12, 6, 4) X(36, 12, 4) X(16, 8, 4) X(8, 4, 4) X(32, 16, 4) X(4, 2, 2) X(6, 2, 2) X(10, 4, 2)
 
-struct StreamPlan {
-  int ok, ns, nt, smem_bytes, generic_total;
-};
 
 template <int NX, int NU, int SPLIT>
 static StreamPlan stream_plan_t(const mimgpu_shape& sh, int stage_fx, int max_smem) {
@@ -198,14 +196,11 @@ static inline int stream_csqp_launch(const KArgs& a, const mimgpu_csqp_params& q
 }
 
 /* ============================================================ SQP / FDDP CTA kernels */
-struct CtaPlan {
-  int ok, nt, smem_bytes, nbuf, ns;
-};
 
-__device__ __noinline__ void sqp_forward_kkt_ool(const Prob& p, double* sm, const Smem& s, double mu, int stage_fx) {
+static __device__ __noinline__ void sqp_forward_kkt_ool(const Prob& p, double* sm, const Smem& s, double mu, int stage_fx) {
   sqp_forward_kkt(p, sm, s, mu, stage_fx);
 }
-__device__ __noinline__ void fddp_expected_improvement_ool(const Prob& p, double* sm, const Smem& s, int feas) {
+static __device__ __noinline__ void fddp_expected_improvement_ool(const Prob& p, double* sm, const Smem& s, int feas) {
   fddp_expected_improvement(p, sm, s, feas);
 }
 

@@ -59,6 +59,8 @@ struct KArgs {
   const int32_t* active;        /* optional subset: block -> problem */
   int32_t n_active;             /* number of blocks that have a problem */
   int32_t stage_fx;             /* 1: Fx_t is staged in shared memory */
+  const double* pack;           /* knot-packed copy of the inputs (kernels_small_gj.cuh), or null */
+  double* spill;                /* knot-packed Vxx Vx K k of the fast SQP kernel, or null */
 };
 
 /* One problem's view. */

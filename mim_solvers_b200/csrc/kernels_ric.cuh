@@ -142,7 +142,7 @@ __device__ __forceinline__ void llt_solve_regs(const double* sL, const double* l
  * loads this kernel has consumed on them so far (load n uses barrier and buffer n & 1 with
  * phase parity (n >> 1) & 1; the count carries over between sweeps of the same kernel). */
 template <int MODE, int NX, int NU>
-__device__ __noinline__ int ric_backward_mma(const Prob& p, double* sm, const RicSmem& s, const RicPar& rp,
+static __device__ __noinline__ int ric_backward_mma(const Prob& p, double* sm, const RicSmem& s, const RicPar& rp,
                                              uint64_t* bars, uint32_t& seq, bool eq_run = false) {
   using C = RicCfg<NX, NU>;
   constexpr int N = C::N, XT = C::XT, NT = C::NT, KT = C::KT, UT = C::UT;

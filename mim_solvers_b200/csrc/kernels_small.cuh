@@ -21,6 +21,7 @@
 #include <cuda_runtime.h>
 
 #include "kernels_generic.cuh"
+#include "kernels_stream.cuh" /* mbarrier / TMA bulk helpers */
 
 namespace mimgpu {
 
@@ -340,15 +341,15 @@ __device__ __forceinline__ int small_backward(const Prob& p, double* sw, int lan
 
 }  // namespace mimgpu
 #include "kernels_small_mma.cuh"
+#include "kernels_small_gj.cuh"
 namespace mimgpu {
 
 /* ------------------------------------------------------------------- forward */
 /* SolverSQP::forwardPass + checkKKTConditions + gap norm (src/sqp.cpp:270-305, 244-268,
  * 229-236).  Lane i < NX owns state row i, lane a < NU control row a, lane c < N column c
  * of [Fx Fu] for the stationarity residual. */
-template <int NX, int NU>
+template <int NX, int NU, class C = SmallCfg<NX, NU>>
 __device__ __forceinline__ void small_forward(const Prob& p, double* sw, int lane, double mu_dynamic) {
-  using C = SmallCfg<NX, NU>;
   constexpr int N = C::N;
   const int T = p.T;
   double* sX = sw + C::oX;
@@ -514,11 +515,98 @@ __global__ void __launch_bounds__(WPB * 32, SmallTune<NX, NU>::MINB) k_sqp_direc
   small_forward<NX, NU>(p, sw, lane, kp.mu_dynamic);
 }
 
+/* Fast variant (kernels_small_gj.cuh): register-resident backward sweep, K k Vxx Vx spilled for
+ * the forward pass only.  8.3 KB of shared memory per warp. */
+template <int NX, int NU> struct GjTune { static constexpr int WPB = 2, MINB = 8; };
+
+template <int NX, int NU, int WPB>
+__global__ void __launch_bounds__(WPB * 32, GjTune<NX, NU>::MINB) k_sqp_direction_small_gj(KArgs a, SqpKPar kp) {
+  extern __shared__ double smem_small[];
+  using C = GjCfg<NX, NU>;
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int slot = blockIdx.x * WPB + wib;
+  if (slot >= a.n_active) return;
+  const int b = a.active ? a.active[slot] : slot;
+  double* sw = smem_small + (size_t)wib * C::WARP;
+  Prob p = bind(a, b);
+  const int T = p.T;
+  const double* pk = a.pack + (size_t)b * C::pack_doubles(T);
+  double* sp = a.spill + (size_t)b * C::spill_doubles(T);
+  const double preg = a.preg_arr ? a.preg_arr[b] : kp.preg;
+  const double dreg = a.dreg_arr ? a.dreg_arr[b] : kp.dreg;
+  const int st = small_backward_gj<NX, NU>(pk, sp, T, sw, lane, preg, dreg, kp.is_feasible);
+  if (lane == 0) { a.status[b] = st; a.qp_iters[b] = 0; }
+  if (st) {
+    double gap = 0.0;
+    for (int e = lane; e < (T + 1) * NX; e += 32) gap += fabs(p.fs[e]);
+    gap = warp_sum(gap);
+    if (lane == 0) {
+      p.scal[MIMGPU_S_GAP_NORM * (size_t)p.B + b] = gap;
+      p.scal[MIMGPU_S_MERIT * (size_t)p.B + b] = p.cost + kp.mu_dynamic * gap;
+    }
+    return;
+  }
+  small_forward_gj<NX, NU>(p, pk, sp, sw, lane, kp.mu_dynamic);
+}
+
+/* Upload-time repack of the field-major C-ABI arrays into knot records (one CTA per knot). */
+template <int NX, int NU>
+__global__ void __launch_bounds__(128) k_pack_knots(KArgs a, double* pack) {
+  using C = GjCfg<NX, NU>;
+  constexpr int N = C::N;
+  const int T = a.sh.T;
+  const size_t b = blockIdx.x / (T + 1);
+  const int t = blockIdx.x % (T + 1);
+  double* dst = pack + b * C::pack_doubles(T) + (size_t)t * C::REC;
+  auto copy = [&](double* d, const double* s, int n) {
+    for (int e = threadIdx.x; e < n; e += blockDim.x) d[e] = s[e];
+  };
+  copy(dst + C::bFs, a.fs + (b * (T + 1) + t) * NX, NX);
+  if (t == T) {
+    copy(dst + C::tLxx, a.LxxT + b * NX * NX, NX * NX);
+    copy(dst + C::tLx, a.LxT + b * NX, NX);
+    return;
+  }
+  const size_t k = b * T + t;
+  copy(dst + C::bH, a.Lxx + k * NX * NX, NX * NX);
+  copy(dst + C::bH + NX * NX, a.Lxu + k * NX * NU, NX * NU);
+  copy(dst + C::bLuu, a.Luu + k * NU * NU, NU * NU);
+  copy(dst + C::bL, a.Lx + k * NX, NX);
+  copy(dst + C::bL + NX, a.Lu + k * NU, NU);
+  copy(dst + C::bF, a.Fx + k * NX * NX, NX * NX);
+  copy(dst + C::bF + NX * NX, a.Fu + k * NX * NU, NX * NU);
+  (void)N;
+}
+
+/* On-demand copy of the spill records into the solver-member arrays Vxx_ Vx_ K_ k_ of the C ABI. */
+template <int NX, int NU>
+__global__ void __launch_bounds__(128) k_unpack_spill(KArgs a) {
+  using C = GjCfg<NX, NU>;
+  const int T = a.sh.T;
+  const size_t b = blockIdx.x / (T + 1);
+  const int t = blockIdx.x % (T + 1);
+  const double* src = a.spill + b * C::spill_doubles(T) + (size_t)t * C::SREC;
+  auto copy = [&](double* d, const double* s, int n) {
+    for (int e = threadIdx.x; e < n; e += blockDim.x) d[e] = s[e];
+  };
+  copy(a.Vxx + (b * (T + 1) + t) * NX * NX, src + C::sV, NX * NX);
+  copy(a.Vx + (b * (T + 1) + t) * NX, src + C::sVx, NX);
+  if (t < T) {
+    copy(a.K + (b * T + t) * NX * NU, src + C::sK, NX * NU);
+    copy(a.kff + (b * T + t) * NU, src + C::sk, NU);
+  }
+}
+
 /* ------------------------------------------------------------------ dispatch */
-/* MIMGPU_SMALL_NOMMA=1 selects the DFMA (CUDA-core) variant of the backward sweep: A/B switch
- * for profiling, both variants are parity-tested. */
+/* MIMGPU_SMALL_NOMMA=1 selects the DFMA (CUDA-core) variant of the full-spill backward sweep and
+ * MIMGPU_SMALL_FULL=1 makes the full-spill kernel the default: A/B switches for profiling, all
+ * variants are parity-tested. */
 static inline bool small_nomma() {
   static const bool v = getenv("MIMGPU_SMALL_NOMMA") != nullptr;
+  return v;
+}
+static inline bool small_force_full() {
+  static const bool v = getenv("MIMGPU_SMALL_FULL") != nullptr || getenv("MIMGPU_SMALL_NOMMA") != nullptr;
   return v;
 }
 
@@ -535,29 +623,103 @@ static int small_launch_t(const KArgs& a, const SqpKPar& kp, cudaStream_t st, bo
   kern<<<grid, WPB * 32, smem, st>>>(a, kp);
   return 0;
 }
+template <int NX, int NU, int WPB>
+static int small_launch_gj_t(const KArgs& a, const SqpKPar& kp, cudaStream_t st, bool configure_only) {
+  if constexpr (NX % 4 == 0) {
+    using C = GjCfg<NX, NU>;
+    const int smem = WPB * C::WARP * (int)sizeof(double);
+    auto kern = k_sqp_direction_small_gj<NX, NU, WPB>;
+    if (configure_only) {
+      if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return 1;
+      cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+      return 0;
+    }
+    const int grid = (a.n_active + WPB - 1) / WPB;
+    kern<<<grid, WPB * 32, smem, st>>>(a, kp);
+    return 0;
+  } else {
+    return -1;
+  }
+}
 
 #define MIMGPU_SMALL_SHAPES(X) X(12, 6) X(8, 4) X(16, 8) X(4, 2) X(6, 2) X(10, 4)
 
-/* 1 when a specialised SQP kernel exists for this shape (and is configured) */
+/* bit 0: a full-spill kernel exists for this shape, bit 1: the fast variant too */
 static inline int small_kernels_configure(const mimgpu_shape& s) {
   KArgs dummy{};
   SqpKPar kp{};
-#define X(NX_, NU_) \
-  if (s.nx == NX_ && s.nu == NU_) return small_launch_t<NX_, NU_, SmallTune<NX_, NU_>::WPB>(dummy, kp, nullptr, true) == 0;
+#define X(NX_, NU_)                                                                                         \
+  if (s.nx == NX_ && s.nu == NU_) {                                                                         \
+    int r = small_launch_t<NX_, NU_, SmallTune<NX_, NU_>::WPB>(dummy, kp, nullptr, true) == 0 ? 1 : 0;      \
+    if (r && small_launch_gj_t<NX_, NU_, GjTune<NX_, NU_>::WPB>(dummy, kp, nullptr, true) == 0) r |= 2;     \
+    return r;                                                                                               \
+  }
   MIMGPU_SMALL_SHAPES(X)
 #undef X
   return 0;
 }
 
-/* 0 when launched, < 0 when no specialisation applies (caller uses the generic kernel) */
-static inline int small_sqp_direction_launch(const KArgs& a, const SqpKPar& kp, int, cudaStream_t st) {
+/* variant 0: fast kernel when it exists (else full), 1: full-spill kernel.  Returns 0 when the
+ * fast kernel was launched, 1 when the full-spill kernel was launched, < 0 when no
+ * specialisation applies (caller uses the generic kernel). */
+static inline int small_sqp_direction_launch(const KArgs& a, const SqpKPar& kp, int variant, cudaStream_t st) {
   /* cp.async needs 16-byte aligned sources: all blocks have even sizes, so only the base
    * pointers matter */
   const uintptr_t al = (uintptr_t)a.Fx | (uintptr_t)a.Fu | (uintptr_t)a.Lxx | (uintptr_t)a.Lxu | (uintptr_t)a.Luu |
                        (uintptr_t)a.Lx | (uintptr_t)a.Lu | (uintptr_t)a.fs | (uintptr_t)a.LxxT;
   if (al & 15) return -1;
-#define X(NX_, NU_) \
-  if (a.sh.nx == NX_ && a.sh.nu == NU_) return small_launch_t<NX_, NU_, SmallTune<NX_, NU_>::WPB>(a, kp, st, false);
+#define X(NX_, NU_)                                                                                          \
+  if (a.sh.nx == NX_ && a.sh.nu == NU_) {                                                                    \
+    if (variant == 0 && !small_force_full() && a.pack && a.spill &&                                         \
+        small_launch_gj_t<NX_, NU_, GjTune<NX_, NU_>::WPB>(a, kp, st, false) == 0)                           \
+      return 0;                                                                                              \
+    return small_launch_t<NX_, NU_, SmallTune<NX_, NU_>::WPB>(a, kp, st, false) == 0 ? 1 : -1;              \
+  }
+  MIMGPU_SMALL_SHAPES(X)
+#undef X
+  return -1;
+}
+
+/* knot-packed buffers of the fast variant: doubles per problem (0: no fast variant for the shape) */
+static inline int small_pack_layout(const mimgpu_shape& s, size_t* pack_doubles, size_t* spill_doubles) {
+  *pack_doubles = 0; *spill_doubles = 0;
+#define X(NX_, NU_)                                                             \
+  if (s.nx == NX_ && s.nu == NU_) {                                             \
+    if constexpr (NX_ % 4 == 0) {                                               \
+      *pack_doubles = GjCfg<NX_, NU_>::pack_doubles(s.T);                       \
+      *spill_doubles = GjCfg<NX_, NU_>::spill_doubles(s.T);                     \
+      return 0;                                                                 \
+    }                                                                           \
+    return -1;                                                                  \
+  }
+  MIMGPU_SMALL_SHAPES(X)
+#undef X
+  return -1;
+}
+/* field-major inputs (a.Fx ...) -> knot records in `pack`, all B problems */
+static inline int small_pack_launch(const KArgs& a, double* pack, cudaStream_t st) {
+#define X(NX_, NU_)                                                                             \
+  if (a.sh.nx == NX_ && a.sh.nu == NU_) {                                                       \
+    if constexpr (NX_ % 4 == 0) {                                                               \
+      k_pack_knots<NX_, NU_><<<(unsigned)a.sh.B * (a.sh.T + 1), 128, 0, st>>>(a, pack);         \
+      return 0;                                                                                 \
+    }                                                                                           \
+    return -1;                                                                                  \
+  }
+  MIMGPU_SMALL_SHAPES(X)
+#undef X
+  return -1;
+}
+/* spill records -> Vxx_ Vx_ K_ k_ arrays of the C ABI, all B problems */
+static inline int small_unpack_launch(const KArgs& a, cudaStream_t st) {
+#define X(NX_, NU_)                                                                             \
+  if (a.sh.nx == NX_ && a.sh.nu == NU_) {                                                       \
+    if constexpr (NX_ % 4 == 0) {                                                               \
+      k_unpack_spill<NX_, NU_><<<(unsigned)a.sh.B * (a.sh.T + 1), 128, 0, st>>>(a);             \
+      return 0;                                                                                 \
+    }                                                                                           \
+    return -1;                                                                                  \
+  }
   MIMGPU_SMALL_SHAPES(X)
 #undef X
   return -1;

@@ -143,7 +143,7 @@ __device__ __forceinline__ double split_reduce(double v) {
 /* SolverCSQP::backwardPass_without_rho_update (src/csqp.cpp:1025-1108), gains deferred to
  * stream_solve_gains.  Writes Vx_, Qu_. */
 template <int NX, int NU, int SPLIT>
-__device__ __noinline__ void stream_backward_light(const Prob& p, double* sm, const StreamSmem& s, Pipe<NX, NU>& pipe,
+static __device__ __noinline__ void stream_backward_light(const Prob& p, double* sm, const StreamSmem& s, Pipe<NX, NU>& pipe,
                                       double sigma) {
   using C = StreamCfg<NX, NU>;
   const int T = p.T, ng = p.ng, ngT = p.ngT, tid = threadIdx.x, nth = blockDim.x;
@@ -288,7 +288,7 @@ __device__ __noinline__ void stream_backward_light(const Prob& p, double* sm, co
 /* k_t = Quu_t^-1 Qu_t for all knots (src/csqp.cpp:1096-1097), one thread per knot, serial
  * substitution in the reference's order. */
 template <int NU>
-__device__ __noinline__ void stream_solve_gains(const Prob& p) {
+static __device__ __noinline__ void stream_solve_gains(const Prob& p) {
   for (int t = threadIdx.x; t < p.T; t += blockDim.x) {
     const double* L = p.L + (size_t)t * NU * NU;
     double x[NU];
@@ -318,7 +318,7 @@ __device__ __noinline__ void stream_solve_gains(const Prob& p) {
 /* SolverCSQP::forwardPass (src/csqp.cpp:630-647) fused with update_lagrangian_parameters
  * (src/csqp.cpp:1196-1340): dx~, du~, z, y, dx_ := dx~, du_ := du~, residual norms. */
 template <int NX, int NU, int SPLIT>
-__device__ __noinline__ void stream_forward_update(const Prob& p, double* sm, const StreamSmem& s, Pipe<NX, NU>& pipe,
+static __device__ __noinline__ void stream_forward_update(const Prob& p, double* sm, const StreamSmem& s, Pipe<NX, NU>& pipe,
                                       const mimgpu_csqp_params& q_, int iter, AdmmNorms& n) {
   using C = StreamCfg<NX, NU>;
   const int T = p.T, ng = p.ng, ngT = p.ngT, tid = threadIdx.x, nth = blockDim.x, lane = tid & 31;
@@ -560,7 +560,7 @@ struct SqpFwdSmem {
  * (src/sqp.cpp:244-268) and the gap norm / merit of computeDirection (src/sqp.cpp:229-236):
  * the knot's Fx, Fu, K, Vxx+ are streamed by TMA NS knots ahead, vectors through registers. */
 template <int NX, int NU, int SPLIT>
-__device__ __noinline__ void stream_sqp_forward(const Prob& p, double* sm, PipeSqp<NX, NU>& pipe, double mu_dynamic) {
+static __device__ __noinline__ void stream_sqp_forward(const Prob& p, double* sm, PipeSqp<NX, NU>& pipe, double mu_dynamic) {
   using S = SqpFwdSmem<NX, NU>;
   constexpr int N = NX + NU, VPT = 3;
   const int T = p.T, tid = threadIdx.x, nth = blockDim.x, lane = tid & 31;

@@ -15,9 +15,7 @@
 #include <string>
 #include <vector>
 
-#include "kernels_generic.cuh"
-#include "kernels_small.cuh"
-#include "kernels_cta.cuh"
+#include "launchers.h"
 
 using namespace mimgpu;
 
@@ -53,7 +51,13 @@ struct mimgpu_ctx {
   int nt = 32;                     /* CTA size of the generic kernels */
   int smem_bytes = 0;
   int sm_count = 148;
-  int use_small = 0;               /* specialised small-shape kernel available */
+  int use_small = 0;               /* specialised small-shape kernels: bit 0 full-spill, bit 1 fast */
+  bool extras_stale = false;       /* Qu / Quuk / LLT not written by the last (fast) SQP direction */
+  bool spill_packed = false;       /* Vxx / Vx / K / k of the last direction live in the spill records */
+  double* pack_buf = nullptr;      /* knot-packed copy of the inputs (fast small-shape kernel) */
+  double* spill_buf = nullptr;     /* knot-packed Vxx Vx K k */
+  size_t pack_pp = 0, spill_pp = 0; /* doubles per problem */
+  SqpKPar last_sqp{};              /* its parameters, for the on-demand recomputation */
   CtaPlan cplan{};                 /* DMMA CTA-per-problem SQP / FDDP kernel (kernels_cta.cuh) */
   StreamPlan splan{};              /* streaming CSQP kernel (kernels_stream.cuh), ok = 0: not available */
 };
@@ -224,9 +228,9 @@ static int configure_launch(mimgpu_ctx* c) {
   CU(cudaFuncSetAttribute(k_sqp_direction_generic, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
   CU(cudaFuncSetAttribute(k_fddp_direction_generic, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
   CU(cudaFuncSetAttribute(k_csqp_direction_generic, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
-  c->use_small = small_kernels_configure(s);
-  c->splan = stream_plan(s, stage, max_smem);
-  c->cplan = cta_plan(s, stage, max_smem);
+  c->use_small = small_kernels_configure_x(s);
+  c->splan = stream_plan_x(s, stage, max_smem);
+  c->cplan = cta_plan_x(s, stage, max_smem);
   return MIMGPU_OK;
 }
 
@@ -277,6 +281,12 @@ int mimgpu_create(mimgpu_ctx** out, int device, const mimgpu_shape* shape) {
   if (e == cudaSuccess) e = cudaMemset(c->ibuf, 0, sizeof(int32_t) * 4 * (size_t)s.B);
   if (e == cudaSuccess) e = cudaMalloc(&c->reg_buf, sizeof(double) * 2 * (size_t)s.B);
   if (e == cudaSuccess) e = cudaMalloc(&c->summary_dev, sizeof(SummaryDev));
+  if (e == cudaSuccess && (c->use_small & 2) &&
+      small_pack_layout_x(s, &c->pack_pp, &c->spill_pp) == 0) {
+    e = cudaMalloc(&c->pack_buf, c->pack_pp * (size_t)s.B * sizeof(double));
+    if (e == cudaSuccess) e = cudaMalloc(&c->spill_buf, c->spill_pp * (size_t)s.B * sizeof(double));
+    if (e == cudaSuccess) e = cudaMemset(c->spill_buf, 0, c->spill_pp * (size_t)s.B * sizeof(double));
+  }
   if (e == cudaSuccess) e = cudaDeviceSynchronize();
   if (e != cudaSuccess) {
     mimgpu_destroy(c);
@@ -285,6 +295,7 @@ int mimgpu_create(mimgpu_ctx** out, int device, const mimgpu_shape* shape) {
   c->k.qp_iters = c->ibuf; c->k.status = c->ibuf + s.B; c->k.converged = c->ibuf + 2 * (size_t)s.B;
   c->k.active = nullptr; c->k.n_active = s.B;
   c->k.preg_arr = nullptr; c->k.dreg_arr = nullptr;
+  c->k.pack = nullptr; c->k.spill = c->spill_buf;
   *out = c;
   return MIMGPU_OK;
 }
@@ -292,7 +303,7 @@ int mimgpu_create(mimgpu_ctx** out, int device, const mimgpu_shape* shape) {
 void mimgpu_destroy(mimgpu_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
-  cudaFree(c->in_buf); cudaFree(c->state_buf); cudaFree(c->ibuf); cudaFree(c->reg_buf); cudaFree(c->summary_dev);
+  cudaFree(c->pack_buf); cudaFree(c->spill_buf); cudaFree(c->in_buf); cudaFree(c->state_buf); cudaFree(c->ibuf); cudaFree(c->reg_buf); cudaFree(c->summary_dev);
   delete c;
 }
 
@@ -303,6 +314,20 @@ int mimgpu_get_shape(const mimgpu_ctx* c, mimgpu_shape* shape) {
 }
 
 /* ------------------------------------------------------------------ data in */
+/* Shapes served by the fast warp-per-problem SQP kernel keep a second, knot-packed copy of the
+ * inputs (one record per knot, kernels_small_gj.cuh): built here, right after the upload, by one
+ * streaming pass on the device (read + write of the inputs at HBM speed). */
+static int pack_inputs(mimgpu_ctx* c, cudaStream_t st) {
+  c->k.pack = nullptr;
+  if (!c->pack_buf || getenv("MIMGPU_FORCE_GENERIC") != nullptr) return MIMGPU_OK;
+  if (small_pack_launch_x(c->k, c->pack_buf, st) != 0) return MIMGPU_OK;
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(MIMGPU_ERR_CUDA, std::string("k_pack_knots: ") + cudaGetErrorString(e));
+  c->launches++;
+  c->k.pack = c->pack_buf;
+  return MIMGPU_OK;
+}
+
 int mimgpu_upload(mimgpu_ctx* c, const mimgpu_derivs* d, int memkind, void* stream) {
   if (!c || !d) return fail(MIMGPU_ERR_INVALID, "null pointer");
   cudaStream_t st = (cudaStream_t)stream;
@@ -318,7 +343,7 @@ int mimgpu_upload(mimgpu_ctx* c, const mimgpu_derivs* d, int memkind, void* stre
   if (memkind == MIMGPU_MEM_DEVICE) {
     for (int i = 0; i < 20; ++i) *slot[i] = n[i] ? src[i] : nullptr;
     c->have_inputs = true;
-    return MIMGPU_OK;
+    return pack_inputs(c, st);
   }
   if (memkind != MIMGPU_MEM_HOST) return fail(MIMGPU_ERR_INVALID, "bad memkind");
   if (!c->in_buf) {
@@ -336,7 +361,7 @@ int mimgpu_upload(mimgpu_ctx* c, const mimgpu_derivs* d, int memkind, void* stre
     p += (n[i] + 1) & ~(size_t)1;
   }
   c->have_inputs = true;
-  return MIMGPU_OK;
+  return pack_inputs(c, st);
 }
 
 int mimgpu_set_reg(mimgpu_ctx* c, const double* preg, const double* dreg, void* stream) {
@@ -411,12 +436,18 @@ int mimgpu_sqp_direction(mimgpu_ctx* c, const mimgpu_sqp_params* p, void* stream
   SqpKPar kp{p->preg, p->dreg, p->mu_dynamic, p->is_feasible};
   cudaStream_t st = (cudaStream_t)stream;
   if (c->use_small && getenv("MIMGPU_FORCE_GENERIC") == nullptr) {
-    rc = small_sqp_direction_launch(c->k, kp, c->sm_count, st);
-    if (rc == 0) return post_launch(c, "k_sqp_direction_small");
-    if (rc > 0) return fail(MIMGPU_ERR_CUDA, "small kernel launch configuration failed");
+    rc = small_sqp_direction_launch_x(c->k, kp, 0, st);
+    if (rc >= 0) {
+      c->extras_stale = (rc == 0);
+      c->spill_packed = (rc == 0);
+      c->last_sqp = kp;
+      return post_launch(c, rc == 0 ? "k_sqp_direction_small_gj" : "k_sqp_direction_small");
+    }
   }
+  c->extras_stale = false;
+  c->spill_packed = false;
   if (c->cplan.ok && !c->use_small && getenv("MIMGPU_FORCE_GENERIC") == nullptr &&
-      (((uintptr_t)c->k.Fx | (uintptr_t)c->k.Fu) & 15) == 0 && cta_sqp_launch(c->k, kp, false, c->cplan, st) == 0)
+      (((uintptr_t)c->k.Fx | (uintptr_t)c->k.Fu) & 15) == 0 && cta_sqp_launch_x(c->k, kp, false, c->cplan, st) == 0)
     return post_launch(c, "k_sqp_direction_cta");
   k_sqp_direction_generic<<<c->k.n_active, c->nt, c->smem_bytes, st>>>(c->k, kp);
   return post_launch(c, "k_sqp_direction_generic");
@@ -428,9 +459,11 @@ int mimgpu_fddp_direction(mimgpu_ctx* c, const mimgpu_sqp_params* p, void* strea
   if (!p) return fail(MIMGPU_ERR_INVALID, "null params");
   if (c->k.n_active == 0) return MIMGPU_OK;
   SqpKPar kp{p->preg, p->dreg, p->mu_dynamic, p->is_feasible};
+  c->extras_stale = false;
+  c->spill_packed = false;
   if (c->cplan.ok && getenv("MIMGPU_FORCE_GENERIC") == nullptr &&
       (((uintptr_t)c->k.Fx | (uintptr_t)c->k.Fu) & 15) == 0 &&
-      cta_sqp_launch(c->k, kp, true, c->cplan, (cudaStream_t)stream) == 0)
+      cta_sqp_launch_x(c->k, kp, true, c->cplan, (cudaStream_t)stream) == 0)
     return post_launch(c, "k_fddp_direction_cta");
   k_fddp_direction_generic<<<c->k.n_active, c->nt, c->smem_bytes, (cudaStream_t)stream>>>(c->k, kp);
   return post_launch(c, "k_fddp_direction_generic");
@@ -465,7 +498,7 @@ int mimgpu_csqp_direction(mimgpu_ctx* c, const mimgpu_csqp_params* p, int with_k
   if (c->splan.ok && getenv("MIMGPU_FORCE_GENERIC") == nullptr) {
     /* TMA bulk copies need 16-byte aligned sources (block sizes are even by construction) */
     const uintptr_t al = (uintptr_t)c->k.Fx | (uintptr_t)c->k.Fu | (uintptr_t)c->k.Gx | (uintptr_t)c->k.Gu;
-    if ((al & 15) == 0 && stream_csqp_launch(c->k, *p, with_kkt, c->splan, (cudaStream_t)stream) == 0)
+    if ((al & 15) == 0 && stream_csqp_launch_x(c->k, *p, with_kkt, c->splan, (cudaStream_t)stream) == 0)
       return post_launch(c, "k_csqp_direction_stream");
   }
   k_csqp_direction_generic<<<c->k.n_active, c->nt, c->smem_bytes, (cudaStream_t)stream>>>(c->k, kp);
@@ -473,10 +506,39 @@ int mimgpu_csqp_direction(mimgpu_ctx* c, const mimgpu_csqp_params* p, int with_k
 }
 
 /* ----------------------------------------------------------------- data out */
+/* Qu_, Quuk_ and Quu_llt_ are solver members the reference keeps per knot but that neither the
+ * SQP forward pass nor its outputs use; the fast small-shape kernel does not spill them.  When
+ * a caller asks for one of them the direction is recomputed by the full-spill kernel (same
+ * inputs, same parameters), once. */
+static int refresh_extras(mimgpu_ctx* c, int field, cudaStream_t st) {
+  if (c->spill_packed && (field == MIMGPU_F_VXX || field == MIMGPU_F_VX || field == MIMGPU_F_K ||
+                          field == MIMGPU_F_KFF)) {
+    /* Vxx_ Vx_ K_ k_ of the fast kernel live in its knot-packed spill records: copy them out once */
+    if (small_unpack_launch_x(c->k, st) != 0) return fail(MIMGPU_ERR_CUDA, "k_unpack_spill launch failed");
+    int rc = post_launch(c, "k_unpack_spill");
+    if (rc) return rc;
+    c->spill_packed = false;
+    return MIMGPU_OK;
+  }
+  if (!c->extras_stale) return MIMGPU_OK;
+  if (field != MIMGPU_F_QU && field != MIMGPU_F_QUUK && field != MIMGPU_F_QUU_LLT) return MIMGPU_OK;
+  if (c->k.n_active > 0) {
+    if (small_sqp_direction_launch_x(c->k, c->last_sqp, 1, st) != 1)
+      return fail(MIMGPU_ERR_CUDA, "full-spill kernel launch failed");
+    int rc = post_launch(c, "k_sqp_direction_small");
+    if (rc) return rc;
+  }
+  c->extras_stale = false;
+  c->spill_packed = false;
+  return MIMGPU_OK;
+}
+
 int mimgpu_download(mimgpu_ctx* c, int field, double* dst, void* stream) {
   if (!c || !dst) return fail(MIMGPU_ERR_INVALID, "null pointer");
   if (field < 0 || field >= MIMGPU_F_COUNT) return fail(MIMGPU_ERR_INVALID, "bad field id");
   CU(cudaSetDevice(c->device));
+  int rc = refresh_extras(c, field, (cudaStream_t)stream);
+  if (rc) return rc;
   if (c->field_n[field])
     CU(cudaMemcpyAsync(dst, c->field[field], c->field_n[field] * sizeof(double), cudaMemcpyDeviceToHost,
                        (cudaStream_t)stream));
@@ -486,6 +548,12 @@ int mimgpu_download(mimgpu_ctx* c, int field, double* dst, void* stream) {
 int mimgpu_field_ptr(mimgpu_ctx* c, int field, double** dev_ptr, int64_t* n_doubles) {
   if (!c) return fail(MIMGPU_ERR_INVALID, "null pointer");
   if (field < 0 || field >= MIMGPU_F_COUNT) return fail(MIMGPU_ERR_INVALID, "bad field id");
+  if (c->extras_stale || c->spill_packed) {
+    CU(cudaSetDevice(c->device));
+    int rc = refresh_extras(c, field, (cudaStream_t)0);
+    if (rc) return rc;
+    CU(cudaStreamSynchronize((cudaStream_t)0));
+  }
   if (dev_ptr) *dev_ptr = c->field[field];
   if (n_doubles) *n_doubles = (int64_t)c->field_n[field];
   return MIMGPU_OK;

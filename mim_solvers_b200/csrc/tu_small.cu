@@ -1,0 +1,17 @@
+/* translation unit of the warp-per-problem SQP kernels */
+#include <cstdlib>
+
+#include "launchers.h"
+#include "kernels_small.cuh"
+
+namespace mimgpu {
+int small_kernels_configure_x(const mimgpu_shape& s) { return small_kernels_configure(s); }
+int small_sqp_direction_launch_x(const KArgs& a, const SqpKPar& kp, int variant, cudaStream_t st) {
+  return small_sqp_direction_launch(a, kp, variant, st);
+}
+int small_pack_layout_x(const mimgpu_shape& s, size_t* pack_doubles, size_t* spill_doubles) {
+  return small_pack_layout(s, pack_doubles, spill_doubles);
+}
+int small_pack_launch_x(const KArgs& a, double* pack, cudaStream_t st) { return small_pack_launch(a, pack, st); }
+int small_unpack_launch_x(const KArgs& a, cudaStream_t st) { return small_unpack_launch(a, st); }
+}  // namespace mimgpu
