@@ -88,6 +88,24 @@ class ClockSampler:
         self.device, self.rows, self._stop, self._t = device, [], threading.Event(), None
 
     def _run(self):
+        try:  # NVML in-process: ~1 ms per sample, so even a 20 ms timed region gets several
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.device)
+            mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            bits = [("hw_slowdown", nv.nvmlClocksThrottleReasonHwSlowdown),
+                    ("hw_thermal_slowdown", nv.nvmlClocksThrottleReasonHwThermalSlowdown),
+                    ("sw_thermal_slowdown", nv.nvmlClocksThrottleReasonSwThermalSlowdown),
+                    ("sw_power_cap", nv.nvmlClocksThrottleReasonSwPowerCap)]
+            while not self._stop.is_set():
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                self.rows.append([str(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)), str(mx),
+                                  str(nv.nvmlDeviceGetPowerUsage(h) / 1000.0)]
+                                 + ["Active" if r & b else "Not Active" for _, b in bits])
+                self._stop.wait(0.002)
+            return
+        except Exception:
+            pass
         while not self._stop.is_set():
             try:
                 out = subprocess.run(["nvidia-smi", "-i", str(self.device), f"--query-gpu={self.Q}",
@@ -261,6 +279,13 @@ def gpu_arm(args, rank, world, local_rank):
             "traffic": None, "peak_source": peak_src, "kernel_ms": kernel_ms,
             "algorithmic_bytes_per_qp": bytes_qp, "flops_per_qp": flops_qp,
             "fp64_tflops_achieved": flops_qp * B / (kernel_ms * 1e-3) / 1e12}
+    tf = ROOT / "profiles" / "traffic_r01.json"   # dram bytes of one launch from the committed ncu --set full capture
+    if tf.exists():
+        tr = json.loads(tf.read_text()).get(args.workload)
+        if tr and tr.get("B") == B:
+            roof["traffic"] = tr["dram_bytes_per_launch"]
+            roof["traffic_source"] = tr["source"]
+            roof["algorithmic_bytes_per_launch"] = bytes_qp * B
     if solver == "csqp" or flops_qp / bytes_qp > 36.8e12 / (hbm_peak * 1e9):
         roof.update(bound="fp64", achieved=roof["fp64_tflops_achieved"], peak=36.8, unit="TFLOP/s",
                     frac=roof["fp64_tflops_achieved"] / 36.8,

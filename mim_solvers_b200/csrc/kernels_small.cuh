@@ -517,7 +517,7 @@ __global__ void __launch_bounds__(WPB * 32, SmallTune<NX, NU>::MINB) k_sqp_direc
 
 /* Fast variant (kernels_small_gj.cuh): register-resident backward sweep, K k Vxx Vx spilled for
  * the forward pass only.  8.3 KB of shared memory per warp. */
-template <int NX, int NU> struct GjTune { static constexpr int WPB = 2, MINB = 8; };
+template <int NX, int NU> struct GjTune { static constexpr int WPB = 2, MINB = 7; };
 
 template <int NX, int NU, int WPB>
 __global__ void __launch_bounds__(WPB * 32, GjTune<NX, NU>::MINB) k_sqp_direction_small_gj(KArgs a, SqpKPar kp) {
