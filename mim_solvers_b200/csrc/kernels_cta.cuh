@@ -59,7 +59,7 @@ k_csqp_direction_stream(KArgs a, StreamKPar kp) {
   pipe.bars = reinterpret_cast<uint64_t*>(sm + ss.bars);
   pipe.stages = sm + ss.uni;
   pipe.stage = ss.stage; pipe.ns = kp.ns; pipe.ng = p.ng;
-  pipe.n_issue = 0; pipe.n_wait = 0;
+  pipe.n_issue = 0; pipe.n_wait = 0; pipe.islot = 0; pipe.wslot = 0; pipe.wphase = 0u;
   if (threadIdx.x == 0) {
     for (int i = 0; i < kp.ns; ++i) mbar_init(pipe.bars + i, 1);
     mbar_init(ric_bars, 1);

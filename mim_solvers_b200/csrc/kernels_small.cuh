@@ -58,11 +58,6 @@ __device__ __forceinline__ void cp_async16(double* smem_dst, const double* gsrc)
   const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gsrc) : "memory");
 }
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int NPEND>
-__device__ __forceinline__ void cp_async_wait() {
-  asm volatile("cp.async.wait_group %0;" ::"n"(NPEND) : "memory");
-}
 /* warp-cooperative copy of NDBL doubles (even, 16-byte aligned on both sides) */
 template <int NDBL>
 __device__ __forceinline__ void warp_stage(double* dst, const double* src, int lane) {

@@ -55,6 +55,15 @@ __device__ __forceinline__ void tma_bulk_g2s(double* dst, const double* src, uin
                "l"(src), "r"(bytes), "r"(smem_u32(bar))
                : "memory");
 }
+/* Ampere-style asynchronous copies for the small per-knot vectors (8 bytes per element) */
+__device__ __forceinline__ void cp_async8(double* smem_dst, const double* gsrc) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int NPEND>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(NPEND) : "memory");
+}
 /* generic-proxy global writes (K, Quu_llt of a full sweep) -> later TMA reads of them */
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async;" ::: "memory"); }
 
@@ -62,6 +71,7 @@ __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.
 template <int NX, int NU>
 struct StreamCfg {
   static constexpr int VPT = 3;  /* vector-pack elements per thread (upper bound) */
+  static constexpr int VD = 4;   /* ring depth of the vector packs (cp.async, VD - 1 knots ahead) */
   /* stage = the knot's matrices, in consumption order */
   __host__ __device__ static int stage_doubles(int ng) { return NX * NX + 2 * NX * NU + ng * (NX + NU); }
   __host__ __device__ static int nv_bwd(int ng) { return 3 * NX + 2 * NU + 3 * ng; }
@@ -69,7 +79,7 @@ struct StreamCfg {
 };
 
 struct StreamSmem {
-  int bars, vec0, vec1, tmp, d, Qx, Qu, Vx, x0, x1, u, dz, yy, red, uni, stage, total;
+  int bars, vec0, nvs, tmp, d, Qx, Qu, Vx, x0, x1, u, dz, yy, red, uni, stage, total;
 };
 template <int NX, int NU>
 __host__ __device__ inline StreamSmem stream_layout(int ng, int ngT, int ns, int generic_total) {
@@ -80,7 +90,8 @@ __host__ __device__ inline StreamSmem stream_layout(int ng, int ngT, int ns, int
   int o = 0;
 #define ST_TAKE(n) (o += (((n) + 1) & ~1), o - (((n) + 1) & ~1))
   s.bars = ST_TAKE(8);
-  s.vec0 = ST_TAKE(nv); s.vec1 = ST_TAKE(nv);
+  constexpr int vd_ = StreamCfg<NX, NU>::VD;
+  s.nvs = nv; s.vec0 = ST_TAKE(vd_ * nv);
   s.tmp = ST_TAKE(NX); s.d = ST_TAKE(ngm); s.Qx = ST_TAKE(NX); s.Qu = ST_TAKE(NU); s.Vx = ST_TAKE(NX);
   s.x0 = ST_TAKE(NX); s.x1 = ST_TAKE(NX); s.u = ST_TAKE(NU); s.dz = ST_TAKE(ngm); s.yy = ST_TAKE(ngm);
   s.red = ST_TAKE(64);
@@ -99,30 +110,38 @@ struct Pipe {
   uint64_t* bars;
   double* stages;
   int stage, ns, ng;
-  uint32_t n_issue, n_wait; /* running load sequence numbers (uniform over the CTA) */
+  uint32_t n_issue, n_wait; /* load sequence numbers since the last reset (kept for the callers that set them) */
+  /* slot / phase of the next issue and of the next wait, advanced without integer division */
+  int islot, wslot;
+  uint32_t wphase;
 
+  /* The elected producer is lane 0 of the LAST warp: in the phases where the sweeps issue, that
+   * warp has no outputs of its own (the mat-vec outputs are dealt to the first warps), so the
+   * ~40 instructions of the five bulk copies are off the other warps' critical path. */
   __device__ __forceinline__ void issue(const Prob& p, int t) {
-    const int slot = n_issue % ns;
-    if (threadIdx.x == 0) {
-      double* dst = stages + (size_t)slot * stage;
-      uint64_t* bar = bars + slot;
+    if (threadIdx.x == blockDim.x - 32) {
+      double* dst = stages + (size_t)islot * stage;
+      uint64_t* bar = bars + islot;
       mbar_expect_tx(bar, (uint32_t)stage * 8u);
-      tma_bulk_g2s(dst, p.Fx + (size_t)t * NX * NX, NX * NX * 8, bar);
-      tma_bulk_g2s(dst + NX * NX, p.Fu + (size_t)t * NX * NU, NX * NU * 8, bar);
-      tma_bulk_g2s(dst + NX * NX + NX * NU, p.K + (size_t)t * NX * NU, NX * NU * 8, bar);
+      const size_t tt = (size_t)t;
+      tma_bulk_g2s(dst, p.Fx + tt * (NX * NX), NX * NX * 8, bar);
+      tma_bulk_g2s(dst + NX * NX, p.Fu + tt * (NX * NU), NX * NU * 8, bar);
+      tma_bulk_g2s(dst + NX * NX + NX * NU, p.K + tt * (NX * NU), NX * NU * 8, bar);
       if (ng) {
-        tma_bulk_g2s(dst + NX * NX + 2 * NX * NU, p.Gx + (size_t)t * ng * NX, (uint32_t)ng * NX * 8, bar);
-        tma_bulk_g2s(dst + NX * NX + 2 * NX * NU + ng * NX, p.Gu + (size_t)t * ng * NU, (uint32_t)ng * NU * 8, bar);
+        tma_bulk_g2s(dst + NX * NX + 2 * NX * NU, p.Gx + tt * (size_t)(ng * NX), (uint32_t)ng * NX * 8, bar);
+        tma_bulk_g2s(dst + NX * NX + 2 * NX * NU + ng * NX, p.Gu + tt * (size_t)(ng * NU), (uint32_t)ng * NU * 8, bar);
       }
     }
+    if (++islot == ns) islot = 0;
     ++n_issue;
   }
   /* all threads: wait for the next stage in consumption order, return its base */
   __device__ __forceinline__ const double* acquire() {
-    const int slot = n_wait % ns;
-    mbar_wait(bars + slot, (n_wait / ns) & 1u);
+    mbar_wait(bars + wslot, wphase);
+    const double* r = stages + (size_t)wslot * stage;
+    if (++wslot == ns) { wslot = 0; wphase ^= 1u; }
     ++n_wait;
-    return stages + (size_t)slot * stage;
+    return r;
   }
 };
 
@@ -148,12 +167,14 @@ static __device__ __noinline__ void stream_backward_light(const Prob& p, double*
   using C = StreamCfg<NX, NU>;
   const int T = p.T, ng = p.ng, ngT = p.ngT, tid = threadIdx.x, nth = blockDim.x;
   double *tmp = sm + s.tmp, *sd = sm + s.d, *sQx = sm + s.Qx, *sQu = sm + s.Qu, *sVx = sm + s.Vx;
-  double* vec[2] = {sm + s.vec0, sm + s.vec1};
+  constexpr int VD = C::VD;
+  double* vecb = sm + s.vec0;
+  const int nvs = s.nvs;
+  auto vecof = [&](int t) -> double* { return vecb + (size_t)(t % VD) * nvs; };
   /* pack of knot t: [Lx NX][dx NX][Vxx_fs NX][Lu NU][du NU][y ng][z ng][rho ng] */
   const int oLx = 0, oDx = NX, oVf = 2 * NX, oLu = 3 * NX, oDu = 3 * NX + NU, oY = 3 * NX + 2 * NU, oZ = oY + ng,
             oR = oZ + ng, nv = oR + ng;
   VecSrc vs[C::VPT];
-  double vr[C::VPT];
 #pragma unroll
   for (int j = 0; j < C::VPT; ++j) {
     const int e = tid + j * nth;
@@ -167,16 +188,22 @@ static __device__ __noinline__ void stream_backward_light(const Prob& p, double*
     else if (e < oR) { vs[j].base = p.z + (e - oZ); vs[j].stride = ng; }
     else if (e < nv) { vs[j].base = p.rho + (e - oR); vs[j].stride = ng; }
   }
+  /* the pack of knot t goes global -> shared memory with 8-byte cp.async, VD - 1 knots ahead of
+   * its consumer (one commit group per knot, empty groups keep the count uniform) */
+  auto issue_pack = [&](int t) {
+    if (t >= 0) {
+      double* dst = vecof(t);
+#pragma unroll
+      for (int j = 0; j < C::VPT; ++j)
+        if (vs[j].base) cp_async8(dst + tid + j * nth, vs[j].base + (size_t)t * vs[j].stride);
+    }
+    cp_async_commit();
+  };
   __syncthreads(); /* every stage and vector buffer is free */
   for (int j = 0; j < pipe.ns - 1; ++j)
     if (T - 1 - j >= 0) pipe.issue(p, T - 1 - j);
-  /* pack of knot T-1 straight to shared memory, pack of knot T-2 into registers */
-#pragma unroll
-  for (int j = 0; j < C::VPT; ++j) {
-    const int e = tid + j * nth;
-    if (vs[j].base) vec[(T - 1) & 1][e] = vs[j].base[(size_t)(T - 1) * vs[j].stride];
-    vr[j] = (vs[j].base && T >= 2) ? vs[j].base[(size_t)(T - 2) * vs[j].stride] : 0.0;
-  }
+  for (int j = 0; j < VD - 1; ++j) issue_pack(T - 1 - j);
+  cp_async_wait<VD - 2>(); /* pack of knot T-1 has landed (made visible by the barrier below) */
   /* terminal knot (src/csqp.cpp:1045-1052) */
   if (ngT) {
     for (int r = tid; r < ngT; r += nth) {
@@ -199,9 +226,9 @@ static __device__ __noinline__ void stream_backward_light(const Prob& p, double*
   }
   __syncthreads(); /* sd (terminal) consumed, pack of knot T-1 visible */
   /* P0 of knot T-1 */
-  for (int i = tid; i < NX; i += nth) tmp[i] = vec[(T - 1) & 1][oVf + i] + sVx[i];
+  for (int i = tid; i < NX; i += nth) tmp[i] = vecof(T - 1)[oVf + i] + sVx[i];
   for (int r = tid; r < ng; r += nth) {
-    const double* v = vec[(T - 1) & 1];
+    const double* v = vecof(T - 1);
     double d = v[oY + r];
     d -= v[oR + r] * v[oZ + r];
     sd[r] = d;
@@ -210,22 +237,11 @@ static __device__ __noinline__ void stream_backward_light(const Prob& p, double*
   for (int t = T - 1; t >= 0; --t) {
     const double* st = pipe.acquire();
     __syncthreads(); /* A: tmp, d visible; knot t+1 completely consumed */
-    if (t - (pipe.ns - 1) >= 0) pipe.issue(p, t - (pipe.ns - 1));
-    if (t >= 1) {
-#pragma unroll
-      for (int j = 0; j < C::VPT; ++j) {
-        const int e = tid + j * nth;
-        if (vs[j].base) vec[(t - 1) & 1][e] = vr[j];
-      }
-      if (t >= 2) {
-#pragma unroll
-        for (int j = 0; j < C::VPT; ++j)
-          if (vs[j].base) vr[j] = vs[j].base[(size_t)(t - 2) * vs[j].stride];
-      }
-    }
+    issue_pack(t - (VD - 1));   /* into the slot of knot t+1, consumed before barrier A */
+    cp_async_wait<VD - 2>();    /* this thread's share of pack t-1 has landed; barrier B publishes it */
     const double *sFx = st, *sFu = st + NX * NX, *sK = st + NX * NX + NX * NU, *sGx = sK + NX * NU,
                  *sGu = sGx + ng * NX;
-    const double* v = vec[t & 1];
+    const double* v = vecof(t);
     /* P1: Qx, Qu (src/csqp.cpp:1068-1093) */
     for (int o0 = 0; o0 < NX + NU; o0 += ngrp) {
       const int o = o0 + grp;
@@ -264,6 +280,8 @@ static __device__ __noinline__ void stream_backward_light(const Prob& p, double*
       }
     }
     __syncthreads(); /* B */
+    /* refill the stage of knot t+1 (free since barrier A) while the last warp has no P2 rows */
+    if (t - (pipe.ns - 1) >= 0) pipe.issue(p, t - (pipe.ns - 1));
     /* P2: Vx = Qx - K^T Qu (src/csqp.cpp:1101-1104); P0 of knot t-1 */
     for (int i = tid; i < NX; i += nth) {
       double acc = 0.0;
@@ -271,10 +289,10 @@ static __device__ __noinline__ void stream_backward_light(const Prob& p, double*
       for (int a = 0; a < NU; ++a) acc = fma(sK[a * NX + i], sQu[a], acc);
       const double vx = sQx[i] - acc;
       p.Vx[(size_t)t * NX + i] = vx;
-      if (t > 0) tmp[i] = vec[(t - 1) & 1][oVf + i] + vx;
+      if (t > 0) tmp[i] = vecof(t - 1)[oVf + i] + vx;
     }
     if (t > 0) {
-      const double* vn = vec[(t - 1) & 1];
+      const double* vn = vecof(t - 1);
       for (int r = tid; r < ng; r += nth) {
         double d = vn[oY + r];
         d -= vn[oR + r] * vn[oZ + r];
@@ -324,7 +342,10 @@ static __device__ __noinline__ void stream_forward_update(const Prob& p, double*
   const int T = p.T, ng = p.ng, ngT = p.ngT, tid = threadIdx.x, nth = blockDim.x, lane = tid & 31;
   double *su = sm + s.u, *sdz = sm + s.dz, *sy = sm + s.yy, *red = sm + s.red;
   double* xs[2] = {sm + s.x0, sm + s.x1};
-  double* vec[2] = {sm + s.vec0, sm + s.vec1};
+  constexpr int VD = C::VD;
+  double* vecb = sm + s.vec0;
+  const int nvs = s.nvs;
+  auto vecof = [&](int t) -> double* { return vecb + (size_t)(t % VD) * nvs; };
   const bool check = (iter % q_.rho_update_interval) == 0;
   const bool heur = q_.update_rho_with_heuristic != 0;
   const double alpha = q_.alpha;
@@ -333,7 +354,6 @@ static __device__ __noinline__ void stream_forward_update(const Prob& p, double*
   const int oK = 0, oFs = NU, oY = NU + NX, oZ = oY + ng, oR = oZ + ng, oG = oR + ng, oLb = oG + ng, oUb = oLb + ng,
             nv = oUb + ng;
   VecSrc vs[C::VPT];
-  double vr[C::VPT];
 #pragma unroll
   for (int j = 0; j < C::VPT; ++j) {
     const int e = tid + j * nth;
@@ -347,16 +367,21 @@ static __device__ __noinline__ void stream_forward_update(const Prob& p, double*
     else if (e < oUb) { vs[j].base = p.glb + (e - oLb); vs[j].stride = ng; }
     else if (e < nv) { vs[j].base = p.gub + (e - oUb); vs[j].stride = ng; }
   }
+  auto issue_pack = [&](int t) { /* 8-byte cp.async, one commit group per knot (see the backward sweep) */
+    if (t < T) {
+      double* dst = vecof(t);
+#pragma unroll
+      for (int j = 0; j < C::VPT; ++j)
+        if (vs[j].base) cp_async8(dst + tid + j * nth, vs[j].base + (size_t)t * vs[j].stride);
+    }
+    cp_async_commit();
+  };
   __syncthreads();
   for (int j = 0; j < pipe.ns - 1; ++j)
     if (j < T) pipe.issue(p, j);
-#pragma unroll
-  for (int j = 0; j < C::VPT; ++j) {
-    const int e = tid + j * nth;
-    if (vs[j].base) vec[0][e] = vs[j].base[0];
-    vr[j] = (vs[j].base && T >= 2) ? vs[j].base[(size_t)vs[j].stride] : 0.0;
-  }
+  for (int j = 0; j < VD - 1; ++j) issue_pack(j);
   for (int i = tid; i < NX; i += nth) xs[0][i] = p.dxt[i];
+  cp_async_wait<VD - 2>(); /* pack of knot 0 */
   __syncthreads();
   const int grp = tid / SPLIT, q = tid % SPLIT, ngrp = nth / SPLIT;
   const int h = lane >> 4, l16 = lane & 15, w16 = (tid >> 5) * 16, n16 = (nth >> 5) * 16;
@@ -366,7 +391,7 @@ static __device__ __noinline__ void stream_forward_update(const Prob& p, double*
                  *sGu = sGx + ng * NX;
     const double* x = xs[t & 1];
     double* xn = xs[(t + 1) & 1];
-    const double* v = vec[t & 1];
+    const double* v = vecof(t);
     /* F1: du~ = -k - K dx~  (src/csqp.cpp:636-637); dx_ := dx~ (src/csqp.cpp:1222-1226, 1241-1242) */
     for (int o0 = 0; o0 < NU; o0 += ngrp) {
       const int a = o0 + grp;
@@ -390,18 +415,8 @@ static __device__ __noinline__ void stream_forward_update(const Prob& p, double*
     for (int i = tid; i < NX; i += nth) p.dx[(size_t)t * NX + i] = x[i];
     __syncthreads(); /* 1: du~ visible; knot t-1 completely consumed */
     if (t + pipe.ns - 1 < T) pipe.issue(p, t + pipe.ns - 1);
-    if (t + 1 < T) {
-#pragma unroll
-      for (int j = 0; j < C::VPT; ++j) {
-        const int e = tid + j * nth;
-        if (vs[j].base) vec[(t + 1) & 1][e] = vr[j];
-      }
-      if (t + 2 < T) {
-#pragma unroll
-        for (int j = 0; j < C::VPT; ++j)
-          if (vs[j].base) vr[j] = vs[j].base[(size_t)(t + 2) * vs[j].stride];
-      }
-    }
+    issue_pack(t + VD - 1);   /* into the slot of knot t-1 */
+    cp_async_wait<VD - 2>();  /* this thread's share of pack t+1 has landed; barrier 2 publishes it */
     /* F2: dx~+ = fs+ + Fx dx~ + Fu du~ (src/csqp.cpp:638-644) and the constraint rows of knot t
      * (src/csqp.cpp:1229-1239); outputs o < NX are states, NX <= o < NX + ng constraint rows;
      * two half-warps share one output (even / odd contraction index) */
@@ -526,9 +541,12 @@ struct PipeSqp {
   double* stages;
   int ns;
   uint32_t n_issue, n_wait;
+  int islot = 0, wslot = 0;     /* slot of the next issue / wait, advanced without integer division */
+  uint32_t wphase = 0u;
   static constexpr int STAGE = 2 * NX * NX + 2 * NX * NU;
   __device__ __forceinline__ void issue(const Prob& p, int t) {
-    const int slot = n_issue % ns;
+    const int slot = islot;
+    if (++islot == ns) islot = 0;
     if (threadIdx.x == 0) {
       double* dst = stages + (size_t)slot * STAGE;
       uint64_t* bar = bars + slot;
@@ -541,8 +559,9 @@ struct PipeSqp {
     ++n_issue;
   }
   __device__ __forceinline__ const double* acquire() {
-    const int slot = n_wait % ns;
-    mbar_wait(bars + slot, (n_wait / ns) & 1u);
+    const int slot = wslot;
+    mbar_wait(bars + slot, wphase);
+    if (++wslot == ns) { wslot = 0; wphase ^= 1u; }
     ++n_wait;
     return stages + (size_t)slot * STAGE;
   }
