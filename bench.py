@@ -159,8 +159,10 @@ def cpu_run(workload: str, solver: str, sample_B: int, steps: int, warmup: int, 
     """Times the oracle's computeDirection over `sample_B` problems, all host threads."""
     oracle = _oracle_native()
     batch = make_workload(workload, sample_B, 0, distinct=min(sample_B, 64))
+    if nthreads <= 0:  # all host cores, whatever OMP_NUM_THREADS says (torchrun sets it to 1)
+        nthreads = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
     o = oracle.Oracle(batch, nthreads=nthreads)
-    cores = oracle.max_threads() if nthreads <= 0 else nthreads
+    cores = nthreads
     if solver == "csqp":
         p = csqp_bench_params()
         o.csqp_calc_norms()
@@ -344,7 +346,7 @@ def gpu_arm(args, rank, world, local_rank):
     if rank != 0:
         return
     cpu = None
-    if not args.no_cpu:
+    if not args.no_cpu and world == 1:
         sample = pick_cpu_sample(args.workload, solver, target_s=1.0)
         r = cpu_run(args.workload, solver, sample, 10, 2)
         cpu = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",

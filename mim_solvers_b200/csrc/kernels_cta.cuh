@@ -157,10 +157,10 @@ static StreamPlan stream_plan_t(const mimgpu_shape& sh, int stage_fx, int max_sm
   if (StreamCfg<NX, NU>::nv_bwd(sh.ng) > nvmax || StreamCfg<NX, NU>::nv_fwd(ngm) > nvmax) return pl;
   for (int ns = 3; ns >= 2; --ns) {
     const StreamSmem ss = stream_layout<NX, NU>(sh.ng, sh.ngT, ns, pl.generic_total);
-    /* three stages only while at least two CTAs still fit an SM */
+    /* more than two stages only while at least two CTAs still fit an SM */
     const int bytes = ss.total * 8;
     if (bytes > max_smem) continue;
-    if (ns == 3 && 2 * (bytes + 1024) > 233472) continue;
+    if (ns >= 3 && 2 * (bytes + 1024) > 233472) continue;
     pl.ns = ns; pl.smem_bytes = bytes;
     if (cudaFuncSetAttribute(k_csqp_direction_stream<NX, NU, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              bytes) != cudaSuccess) {

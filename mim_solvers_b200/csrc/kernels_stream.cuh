@@ -55,6 +55,13 @@ __device__ __forceinline__ void tma_bulk_g2s(double* dst, const double* src, uin
                "l"(src), "r"(bytes), "r"(smem_u32(bar))
                : "memory");
 }
+/* A `double*` that reaches a __noinline__ function as a parameter is a GENERIC pointer: the compiler
+ * then emits LD.E with 64-bit address arithmetic instead of LDS.  Round-tripping it through the
+ * shared window tells the address-space inference what it points to. */
+template <class T>
+__device__ __forceinline__ T* as_shared(T* p) {
+  return reinterpret_cast<T*>(__cvta_shared_to_generic(__cvta_generic_to_shared(const_cast<void*>(static_cast<const void*>(p)))));
+}
 /* Ampere-style asynchronous copies for the small per-knot vectors (8 bytes per element) */
 __device__ __forceinline__ void cp_async8(double* smem_dst, const double* gsrc) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(smem_dst)), "l"(gsrc) : "memory");
@@ -135,6 +142,14 @@ struct Pipe {
     if (++islot == ns) islot = 0;
     ++n_issue;
   }
+  /* same, returning the slot index (callers that address the stage from the shared array itself) */
+  __device__ __forceinline__ int acquire_slot() {
+    mbar_wait(bars + wslot, wphase);
+    const int r = wslot;
+    if (++wslot == ns) { wslot = 0; wphase ^= 1u; }
+    ++n_wait;
+    return r;
+  }
   /* all threads: wait for the next stage in consumption order, return its base */
   __device__ __forceinline__ const double* acquire() {
     mbar_wait(bars + wslot, wphase);
@@ -165,6 +180,8 @@ template <int NX, int NU, int SPLIT>
 static __device__ __noinline__ void stream_backward_light(const Prob& p, double* sm, const StreamSmem& s, Pipe<NX, NU>& pipe,
                                       double sigma) {
   using C = StreamCfg<NX, NU>;
+  extern __shared__ __align__(16) double sm_stream[]; /* the same dynamic array the kernel declares: keeps LDS/STS */
+  sm = sm_stream;
   const int T = p.T, ng = p.ng, ngT = p.ngT, tid = threadIdx.x, nth = blockDim.x;
   double *tmp = sm + s.tmp, *sd = sm + s.d, *sQx = sm + s.Qx, *sQu = sm + s.Qu, *sVx = sm + s.Vx;
   constexpr int VD = C::VD;
@@ -235,7 +252,7 @@ static __device__ __noinline__ void stream_backward_light(const Prob& p, double*
   }
   const int grp = tid / SPLIT, q = tid % SPLIT, ngrp = nth / SPLIT;
   for (int t = T - 1; t >= 0; --t) {
-    const double* st = pipe.acquire();
+    const double* st = sm + s.uni + pipe.acquire_slot() * s.stage;
     __syncthreads(); /* A: tmp, d visible; knot t+1 completely consumed */
     issue_pack(t - (VD - 1));   /* into the slot of knot t+1, consumed before barrier A */
     cp_async_wait<VD - 2>();    /* this thread's share of pack t-1 has landed; barrier B publishes it */
@@ -339,6 +356,8 @@ template <int NX, int NU, int SPLIT>
 static __device__ __noinline__ void stream_forward_update(const Prob& p, double* sm, const StreamSmem& s, Pipe<NX, NU>& pipe,
                                       const mimgpu_csqp_params& q_, int iter, AdmmNorms& n) {
   using C = StreamCfg<NX, NU>;
+  extern __shared__ __align__(16) double sm_stream[]; /* the same dynamic array the kernel declares: keeps LDS/STS */
+  sm = sm_stream;
   const int T = p.T, ng = p.ng, ngT = p.ngT, tid = threadIdx.x, nth = blockDim.x, lane = tid & 31;
   double *su = sm + s.u, *sdz = sm + s.dz, *sy = sm + s.yy, *red = sm + s.red;
   double* xs[2] = {sm + s.x0, sm + s.x1};
@@ -386,7 +405,7 @@ static __device__ __noinline__ void stream_forward_update(const Prob& p, double*
   const int grp = tid / SPLIT, q = tid % SPLIT, ngrp = nth / SPLIT;
   const int h = lane >> 4, l16 = lane & 15, w16 = (tid >> 5) * 16, n16 = (nth >> 5) * 16;
   for (int t = 0; t < T; ++t) {
-    const double* st = pipe.acquire();
+    const double* st = sm + s.uni + pipe.acquire_slot() * s.stage;
     const double *sFx = st, *sFu = st + NX * NX, *sK = st + NX * NX + NX * NU, *sGx = sK + NX * NU,
                  *sGu = sGx + ng * NX;
     const double* x = xs[t & 1];

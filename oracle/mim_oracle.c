@@ -997,8 +997,14 @@ int ora_max_threads(void) {
 }
 
 static int nthreads_of(int n) {
+  /* n <= 0: OpenMP's default team (honours OMP_NUM_THREADS); n > 0: exactly n, capped by the
+   * number of processors (torchrun exports OMP_NUM_THREADS=1, the timed CPU arm asks explicitly) */
   int m = ora_max_threads();
-  return (n <= 0 || n > m) ? m : n;
+  if (n <= 0) return m;
+#ifdef _OPENMP
+  m = omp_get_num_procs();
+#endif
+  return n > m ? m : n;
 }
 
 #define ORA_PARALLEL_BEGIN(s, nthreads)                                      \
