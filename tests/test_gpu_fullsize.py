@@ -1,0 +1,107 @@
+"""GPU: the BASELINE.json configurations at (or near) their full sizes.
+
+The oracle is too slow for whole batches of the large configs, so each test checks
+  (1) the fixed-seed parity subset (the first problems of the batch) against the
+      oracle at 1e-9, with identical status / qp_iters, and
+  (2) size-independent properties on EVERY problem of the batch, recomputed with numpy from
+      the downloaded members: the direction satisfies the linearised dynamics
+      dx_{t+1} = Fx dx_t + Fu du_t + fs_{t+1} (src/sqp.cpp:287-289), du_t = -K_t dx_t - k_t
+      (:285-286), and the reported KKT_ equals the residual of src/sqp.cpp:244-268 evaluated
+      from lag_mul_.
+"""
+import numpy as np
+import pytest
+
+from helpers import assert_close
+from mim_solvers_b200 import _capi
+from mim_solvers_b200.problems import make_config, tile_batch
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-9
+
+
+@pytest.fixture(scope="module")
+def eng():
+    from mim_solvers_b200.engine import BatchEngine
+    _capi.load_library()
+    return BatchEngine
+
+
+def _rel(a, b):
+    return np.abs(a - b).max() / max(1.0, np.abs(b).max())
+
+
+def _sqp_properties(batch, g):
+    dx, du, lam = g.field("dx"), g.field("du"), g.field("lag_mul")
+    Fx, Fu, fs = batch.mat("Fx"), batch.mat("Fu"), batch.arrays["fs"]
+    nxt = np.einsum("btij,btj->bti", Fx, dx[:, :-1]) + np.einsum("btij,btj->bti", Fu, du) + fs[:, 1:]
+    assert _rel(dx[:, 1:], nxt) <= TOL, "linearised dynamics"
+    assert np.abs(dx[:, 0]).max() == 0.0
+    K, k = g.field("K"), g.field("k")
+    assert _rel(du, -np.einsum("btai,bti->bta", K, dx[:, :-1]) - k) <= TOL, "feedback law"
+    rx = batch.arrays["Lx"] + np.einsum("btji,btj->bti", Fx, lam[:, 1:]) - lam[:, :-1]
+    ru = batch.arrays["Lu"] + np.einsum("btji,btj->bti", Fu, lam[:, 1:])
+    kkt = np.maximum(np.abs(rx).max(axis=(1, 2)), np.abs(ru).max(axis=(1, 2)))
+    kkt = np.maximum(kkt, np.abs(batch.arrays["LxT"] - lam[:, -1]).max(axis=1))
+    kkt = np.maximum(kkt, np.abs(fs).max(axis=(1, 2)))
+    got = g.scalar("KKT")
+    assert np.all(np.abs(got - kkt) <= 1e-9 * np.maximum(1.0, kkt)), "KKT residual"
+    assert np.all(np.abs(g.scalar("gap_norm") - np.abs(fs).sum(axis=(1, 2))) <= 1e-9 * np.abs(fs).sum(axis=(1, 2)))
+
+
+@pytest.mark.parametrize("name,B,nsub", [("C2_ur5_sqp", 4096, 64), ("C1_ur5_sqp", 4096, 64), ("C4_lq_nx16", 2048, 32),
+                                         ("C4_lq_nx64", 96, 4), ("C5_talos_sqp", 32, 2)])
+def test_fullsize_sqp(eng, oracle_lib, name, B, nsub):
+    batch = make_config(name, B)
+    g = eng(batch)
+    g.sqp_direction()
+    assert not g.status.any()
+    sub = batch.subset(np.arange(nsub))
+    o = oracle_lib.Oracle(sub)
+    o.sqp_direction()
+    for f in ("dx", "du", "lag_mul", "Vxx", "Vx", "K", "k"):
+        assert_close(g.field(f)[:nsub], o.field(f), TOL, f"{name} {f}")
+    for s in ("KKT", "gap_norm", "merit", "x_grad_norm", "u_grad_norm"):
+        assert_close(g.scalar(s)[:nsub], o.scalar(s), TOL, f"{name} {s}")
+    _sqp_properties(batch, g)
+
+
+@pytest.mark.parametrize("name,B,nsub", [("C1_ur5_csqp", 512, 16), ("C3_solo12_csqp", 64, 4), ("C3b_solo12_bench", 64, 4)])
+def test_fullsize_csqp_protocol(eng, oracle_lib, name, B, nsub):
+    """The benchmark protocol (benchmarks/solo12.cpp:213-216: 50 ADMM iterations, eps = 0, no
+    equality-QP guess) on the bench's own generator; every problem runs the 50 iterations, the
+    projected z respects the bounds, y and z are complementary in sign, and the forward roll-out
+    satisfies the linearised dynamics."""
+    batch = make_config(name, B)
+    p = _capi.default_csqp_params(eps_abs=0.0, eps_rel=0.0, max_qp_iters=50, equality_qp_initial_guess=0)
+    g = eng(batch)
+    g.csqp_calc_norms(); g.csqp_reset_rho(p)
+    g.csqp_direction(p, with_kkt=True)
+    assert not g.status.any() and np.all(g.qp_iters == 51)
+    sub = batch.subset(np.arange(nsub))
+    o = oracle_lib.Oracle(sub)
+    o.csqp_calc_norms(); o.csqp_reset_rho(p)
+    o.csqp_direction(p, with_kkt=True)
+    assert np.array_equal(np.asarray(o.qp_iters), g.qp_iters[:nsub])
+    for f in ("dx_tilde", "du_tilde", "lag_mul", "y", "z", "rho_vec"):
+        assert_close(g.field(f)[:nsub], o.field(f), TOL, f"{name} {f}")
+    for s in ("KKT", "rho_sparse", "norm_primal", "norm_dual"):
+        assert_close(g.scalar(s)[:nsub], o.scalar(s), TOL, f"{name} {s}")
+    dxt, dut = g.field("dx_tilde"), g.field("du_tilde")
+    nxt = np.einsum("btij,btj->bti", batch.mat("Fx"), dxt[:, :-1]) + np.einsum("btij,btj->bti", batch.mat("Fu"), dut) \
+        + batch.arrays["fs"][:, 1:]
+    assert _rel(dxt[:, 1:], nxt) <= TOL
+    T, ng = batch.T, batch.ng
+    z = g.field("z")[:, :T * ng].reshape(B, T, ng)
+    lo, hi = batch.arrays["g_lb"] - batch.arrays["g"], batch.arrays["g_ub"] - batch.arrays["g"]
+    assert np.all(z >= lo - 1e-12 * np.maximum(1.0, np.abs(lo))) and np.all(z <= hi + 1e-12 * np.maximum(1.0, np.abs(hi)))
+
+
+def test_fullsize_tiled_batches_are_identical(eng):
+    """Problems are independent: a batch made of 8 copies of 512 problems returns 8 identical
+    blocks bit for bit (no cross-problem state, no dependence on the slot a problem lands in)."""
+    base = make_config("C2_ur5_sqp", 512)
+    g = eng(tile_batch(base, 4096))
+    g.sqp_direction()
+    dx = g.field("dx").reshape(8, 512, -1)
+    assert all(np.array_equal(dx[0], dx[i]) for i in range(1, 8))
