@@ -315,6 +315,10 @@ def gpu_arm(args, rank, world, local_rank):
         d2h = sum(t.numel() * 8 for t in outs.values()) + B * 8
 
         def e2e_step():
+            if solver == "sqp":   # upload + direction + download in overlapped slices, one C-ABI call
+                eng2.sqp_direction_host(pinned, p, dx=outs["dx"].numpy(), du=outs["du"].numpy(),
+                                        lag_mul=outs["lag_mul"].numpy(), kkt=kkt.numpy(), n_chunks=args.e2e_chunks)
+                return
             eng2.upload(pinned)
             if solver == "csqp":
                 eng2.csqp_calc_norms()
@@ -340,6 +344,8 @@ def gpu_arm(args, rank, world, local_rank):
         dt = allreduce_max((time.perf_counter() - t0) / n_e2e, device=dev)
         e2e = {"value": world * B / dt, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                "d2h_bytes_per_step": int(d2h), "ms_per_step": dt * 1e3, "steps": n_e2e,
+               "call": "mimgpu_sqp_direction_host (%d overlapped slices)" % args.e2e_chunks if solver == "sqp"
+                       else "mimgpu_upload + csqp_direction + mimgpu_download",
                "max_kkt": float(kkt.max())}
         del keep
 
@@ -379,6 +385,7 @@ def main():
     ap.add_argument("--batch", type=int, default=0, help="problems per GPU (default: the workload's)")
     ap.add_argument("--distinct", type=int, default=4096, help="independently drawn problems per GPU")
     ap.add_argument("--e2e-steps", type=int, default=5)
+    ap.add_argument("--e2e-chunks", type=int, default=8, help="slices of the overlapped host path (SQP)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--qp-iters", type=int, default=50, help="ADMM iterations per CSQP QP (protocol: 50)")

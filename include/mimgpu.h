@@ -219,6 +219,16 @@ int mimgpu_set_field(mimgpu_ctx* ctx, int field, const double* src,
 int mimgpu_sqp_direction(mimgpu_ctx* ctx, const mimgpu_sqp_params* p,
                          void* cuda_stream);
 
+/* The same computeDirection for HOST-resident derivatives, end to end (the call a solver makes
+ * right after problem_->calcDiff when the data lives in the ActionData objects): upload, solve and
+ * download of dx_ / du_ / lag_mul_ [B][..] and KKT_ [B] (any of them may be NULL) in `n_chunks`
+ * slices of the batch on two internal streams, so that the PCIe copies of both directions overlap
+ * each other and the kernels.  Synchronous: returns when the host arrays are filled.  Pin the
+ * host memory.  Results are those of mimgpu_upload + mimgpu_sqp_direction + mimgpu_download. */
+int mimgpu_sqp_direction_host(mimgpu_ctx* ctx, const mimgpu_derivs* host_derivs,
+                              const mimgpu_sqp_params* p, double* dx, double* du,
+                              double* lag_mul, double* kkt, int32_t n_chunks);
+
 /* SolverFDDP::computeDirection (src/fddp.cpp:189-204) without calcDiff +
  * updateExpectedImprovement (src/fddp.cpp:256-279): backward pass, gap_norm_,
  * dg_, dq_.  Vxx, Vx, K, k, Qu, Quuk stay on the device for download. */

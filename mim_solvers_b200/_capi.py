@@ -106,7 +106,7 @@ SYMBOLS = (
     "mimgpu_abi_version", "mimgpu_device_count", "mimgpu_last_error", "mimgpu_create",
     "mimgpu_destroy", "mimgpu_get_shape", "mimgpu_upload", "mimgpu_set_reg",
     "mimgpu_set_active", "mimgpu_set_field", "mimgpu_sqp_direction",
-    "mimgpu_fddp_direction", "mimgpu_csqp_calc_norms", "mimgpu_csqp_reset_rho",
+    "mimgpu_sqp_direction_host", "mimgpu_fddp_direction", "mimgpu_csqp_calc_norms", "mimgpu_csqp_reset_rho",
     "mimgpu_csqp_direction", "mimgpu_download", "mimgpu_field_ptr", "mimgpu_scalar",
     "mimgpu_iters_status", "mimgpu_converged", "mimgpu_summary_reduce", "mimgpu_launch_count", "mimgpu_stream_sync", "mimgpu_measure_peaks",
 )
@@ -128,6 +128,7 @@ def _declare(lib):
     lib.mimgpu_set_active.argtypes = [vp, vp, i32, vp]
     lib.mimgpu_set_field.argtypes = [vp, C.c_int, vp, vp]
     lib.mimgpu_sqp_direction.argtypes = [vp, C.POINTER(SqpParams), vp]
+    lib.mimgpu_sqp_direction_host.argtypes = [vp, C.POINTER(Derivs), C.POINTER(SqpParams), vp, vp, vp, vp, i32]
     lib.mimgpu_fddp_direction.argtypes = [vp, C.POINTER(SqpParams), vp]
     lib.mimgpu_csqp_calc_norms.argtypes = [vp, vp]
     lib.mimgpu_csqp_reset_rho.argtypes = [vp, C.POINTER(CsqpParams), vp]

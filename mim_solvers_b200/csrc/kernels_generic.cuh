@@ -61,6 +61,8 @@ struct KArgs {
   int32_t stage_fx;             /* 1: Fx_t is staged in shared memory */
   const double* pack;           /* knot-packed copy of the inputs (kernels_small_gj.cuh), or null */
   double* spill;                /* knot-packed Vxx Vx K k of the fast SQP kernel, or null */
+  int32_t first;                /* first problem of the slice when `active` is null (chunked host path) */
+  int32_t pad_;
 };
 
 /* One problem's view. */

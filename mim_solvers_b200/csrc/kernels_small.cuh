@@ -521,7 +521,7 @@ __global__ void __launch_bounds__(WPB * 32, GjTune<NX, NU>::MINB) k_sqp_directio
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const int slot = blockIdx.x * WPB + wib;
   if (slot >= a.n_active) return;
-  const int b = a.active ? a.active[slot] : slot;
+  const int b = a.active ? a.active[slot] : slot + a.first;
   double* sw = smem_small + (size_t)wib * C::WARP;
   Prob p = bind(a, b);
   const int T = p.T;
@@ -546,11 +546,11 @@ __global__ void __launch_bounds__(WPB * 32, GjTune<NX, NU>::MINB) k_sqp_directio
 
 /* Upload-time repack of the field-major C-ABI arrays into knot records (one CTA per knot). */
 template <int NX, int NU>
-__global__ void __launch_bounds__(128) k_pack_knots(KArgs a, double* pack) {
+__global__ void __launch_bounds__(128) k_pack_knots(KArgs a, double* pack, int b0) {
   using C = GjCfg<NX, NU>;
   constexpr int N = C::N;
   const int T = a.sh.T;
-  const size_t b = blockIdx.x / (T + 1);
+  const size_t b = (size_t)b0 + blockIdx.x / (T + 1);
   const int t = blockIdx.x % (T + 1);
   double* dst = pack + b * C::pack_doubles(T) + (size_t)t * C::REC;
   auto copy = [&](double* d, const double* s, int n) {
@@ -691,12 +691,12 @@ static inline int small_pack_layout(const mimgpu_shape& s, size_t* pack_doubles,
 #undef X
   return -1;
 }
-/* field-major inputs (a.Fx ...) -> knot records in `pack`, all B problems */
-static inline int small_pack_launch(const KArgs& a, double* pack, cudaStream_t st) {
+/* field-major inputs (a.Fx ...) -> knot records in `pack`, problems [b0, b0 + nb) */
+static inline int small_pack_launch(const KArgs& a, double* pack, int b0, int nb, cudaStream_t st) {
 #define X(NX_, NU_)                                                                             \
   if (a.sh.nx == NX_ && a.sh.nu == NU_) {                                                       \
     if constexpr (NX_ % 4 == 0) {                                                               \
-      k_pack_knots<NX_, NU_><<<(unsigned)a.sh.B * (a.sh.T + 1), 128, 0, st>>>(a, pack);         \
+      k_pack_knots<NX_, NU_><<<(unsigned)nb * (a.sh.T + 1), 128, 0, st>>>(a, pack, b0);         \
       return 0;                                                                                 \
     }                                                                                           \
     return -1;                                                                                  \

@@ -24,7 +24,7 @@ int small_sqp_direction_launch_x(const KArgs& a, const SqpKPar& kp, int variant,
 /* knot-packed HBM layout of the fast variant: sizes (doubles per problem), repack of the field-major
  * inputs at upload time, on-demand copy of the spill records into the Vxx_ Vx_ K_ k_ arrays */
 int small_pack_layout_x(const mimgpu_shape& s, size_t* pack_doubles, size_t* spill_doubles);
-int small_pack_launch_x(const KArgs& a, double* pack, cudaStream_t st);
+int small_pack_launch_x(const KArgs& a, double* pack, int b0, int nb, cudaStream_t st);
 int small_unpack_launch_x(const KArgs& a, cudaStream_t st);
 /* streaming CSQP kernel (kernels_stream.cuh, kernels_cta.cuh) */
 StreamPlan stream_plan_x(const mimgpu_shape& sh, int stage_fx, int max_smem);

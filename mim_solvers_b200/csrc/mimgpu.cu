@@ -57,6 +57,7 @@ struct mimgpu_ctx {
   double* pack_buf = nullptr;      /* knot-packed copy of the inputs (fast small-shape kernel) */
   double* spill_buf = nullptr;     /* knot-packed Vxx Vx K k */
   size_t pack_pp = 0, spill_pp = 0; /* doubles per problem */
+  cudaStream_t pipe_st[2] = {nullptr, nullptr}; /* internal streams of the chunked host path */
   SqpKPar last_sqp{};              /* its parameters, for the on-demand recomputation */
   CtaPlan cplan{};                 /* DMMA CTA-per-problem SQP / FDDP kernel (kernels_cta.cuh) */
   StreamPlan splan{};              /* streaming CSQP kernel (kernels_stream.cuh), ok = 0: not available */
@@ -295,7 +296,7 @@ int mimgpu_create(mimgpu_ctx** out, int device, const mimgpu_shape* shape) {
   c->k.qp_iters = c->ibuf; c->k.status = c->ibuf + s.B; c->k.converged = c->ibuf + 2 * (size_t)s.B;
   c->k.active = nullptr; c->k.n_active = s.B;
   c->k.preg_arr = nullptr; c->k.dreg_arr = nullptr;
-  c->k.pack = nullptr; c->k.spill = c->spill_buf;
+  c->k.pack = nullptr; c->k.spill = c->spill_buf; c->k.first = 0; c->k.pad_ = 0;
   *out = c;
   return MIMGPU_OK;
 }
@@ -303,6 +304,8 @@ int mimgpu_create(mimgpu_ctx** out, int device, const mimgpu_shape* shape) {
 void mimgpu_destroy(mimgpu_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
+  if (c->pipe_st[0]) cudaStreamDestroy(c->pipe_st[0]);
+  if (c->pipe_st[1]) cudaStreamDestroy(c->pipe_st[1]);
   cudaFree(c->pack_buf); cudaFree(c->spill_buf); cudaFree(c->in_buf); cudaFree(c->state_buf); cudaFree(c->ibuf); cudaFree(c->reg_buf); cudaFree(c->summary_dev);
   delete c;
 }
@@ -320,7 +323,7 @@ int mimgpu_get_shape(const mimgpu_ctx* c, mimgpu_shape* shape) {
 static int pack_inputs(mimgpu_ctx* c, cudaStream_t st) {
   c->k.pack = nullptr;
   if (!c->pack_buf || getenv("MIMGPU_FORCE_GENERIC") != nullptr) return MIMGPU_OK;
-  if (small_pack_launch_x(c->k, c->pack_buf, st) != 0) return MIMGPU_OK;
+  if (small_pack_launch_x(c->k, c->pack_buf, 0, c->sh.B, st) != 0) return MIMGPU_OK;
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(MIMGPU_ERR_CUDA, std::string("k_pack_knots: ") + cudaGetErrorString(e));
   c->launches++;
@@ -451,6 +454,95 @@ int mimgpu_sqp_direction(mimgpu_ctx* c, const mimgpu_sqp_params* p, void* stream
     return post_launch(c, "k_sqp_direction_cta");
   k_sqp_direction_generic<<<c->k.n_active, c->nt, c->smem_bytes, st>>>(c->k, kp);
   return post_launch(c, "k_sqp_direction_generic");
+}
+
+/* SolverSQP::computeDirection for HOST-resident derivatives, end to end: the batch is cut into
+ * `n_chunks` slices; slice i is uploaded, repacked, solved and its dx_ / du_ / lag_mul_ / KKT_
+ * downloaded on one of two internal streams, so the PCIe copies of both directions overlap each
+ * other and the kernels of the neighbouring slices.  Same results as mimgpu_upload +
+ * mimgpu_sqp_direction + mimgpu_download; returns after everything has landed in the host
+ * arrays (pin them).  Falls back to that sequence when the shape has no sliceable kernel. */
+int mimgpu_sqp_direction_host(mimgpu_ctx* c, const mimgpu_derivs* d, const mimgpu_sqp_params* p, double* dx,
+                              double* du, double* lag_mul, double* kkt, int32_t n_chunks) {
+  if (!c || !d || !p) return fail(MIMGPU_ERR_INVALID, "null pointer");
+  CU(cudaSetDevice(c->device));
+  const mimgpu_shape& sh = c->sh;
+  const size_t B = sh.B, T = sh.T, nx = sh.nx, nu = sh.nu;
+  const bool sliceable = c->pack_buf && (c->use_small & 2) && getenv("MIMGPU_FORCE_GENERIC") == nullptr &&
+                         getenv("MIMGPU_SMALL_FULL") == nullptr && getenv("MIMGPU_SMALL_NOMMA") == nullptr &&
+                         !c->k.active;
+  if (!sliceable || n_chunks <= 1) {
+    int rc = mimgpu_upload(c, d, MIMGPU_MEM_HOST, nullptr);
+    if (rc == MIMGPU_OK) rc = mimgpu_sqp_direction(c, p, nullptr);
+    if (rc == MIMGPU_OK && dx) rc = mimgpu_download(c, MIMGPU_F_DX, dx, nullptr);
+    if (rc == MIMGPU_OK && du) rc = mimgpu_download(c, MIMGPU_F_DU, du, nullptr);
+    if (rc == MIMGPU_OK && lag_mul) rc = mimgpu_download(c, MIMGPU_F_LAG_MUL, lag_mul, nullptr);
+    if (rc == MIMGPU_OK && kkt) rc = mimgpu_scalar(c, MIMGPU_S_KKT, kkt, nullptr);
+    if (rc == MIMGPU_OK) CU(cudaStreamSynchronize(nullptr));
+    return rc;
+  }
+  if ((size_t)n_chunks > B) n_chunks = (int32_t)B;
+  for (int i = 0; i < 2; ++i)
+    if (!c->pipe_st[i]) CU(cudaStreamCreateWithFlags(&c->pipe_st[i], cudaStreamNonBlocking));
+  size_t n[20];
+  const size_t tot = deriv_sizes(sh, n);
+  const double* src[20] = {d->Fx, d->Fu, d->Lxx, d->Lxu, d->Luu, d->Lx, d->Lu, d->fs, d->LxxT, d->LxT,
+                           d->Gx, d->Gu, d->g, d->g_lb, d->g_ub, d->GxT, d->gT, d->g_lbT, d->g_ubT, d->cost};
+  for (int i = 0; i < 19; ++i)
+    if (n[i] && !src[i]) return fail(MIMGPU_ERR_INVALID, "missing derivative array #" + std::to_string(i));
+  if (!c->in_buf) {
+    CU(cudaMalloc(&c->in_buf, tot * sizeof(double)));
+    c->in_doubles = tot;
+  }
+  const double** slot[20];
+  deriv_slots(c->k, slot);
+  double* dst[20];
+  {
+    double* q = c->in_buf;
+    for (int i = 0; i < 20; ++i) {
+      dst[i] = q;
+      *slot[i] = (n[i] && src[i]) ? q : nullptr;
+      q += (n[i] + 1) & ~(size_t)1;
+    }
+  }
+  CU(cudaDeviceSynchronize()); /* earlier work of this ctx on other streams is done with the buffers */
+  SqpKPar kp{p->preg, p->dreg, p->mu_dynamic, p->is_feasible};
+  KArgs ka = c->k;
+  ka.pack = c->pack_buf;
+  const size_t per = (B + n_chunks - 1) / n_chunks;
+  for (size_t b0 = 0, ci = 0; b0 < B; b0 += per, ++ci) {
+    const size_t nb = (b0 + per <= B) ? per : B - b0;
+    cudaStream_t st = c->pipe_st[ci & 1];
+    for (int i = 0; i < 20; ++i) {
+      if (!(n[i] && src[i])) continue;
+      const size_t pb = n[i] / B; /* doubles per problem of this field */
+      CU(cudaMemcpyAsync(dst[i] + b0 * pb, src[i] + b0 * pb, nb * pb * sizeof(double), cudaMemcpyHostToDevice, st));
+    }
+    if (small_pack_launch_x(ka, c->pack_buf, (int)b0, (int)nb, st) != 0)
+      return fail(MIMGPU_ERR_CUDA, "k_pack_knots launch failed");
+    c->launches++;
+    ka.first = (int32_t)b0;
+    ka.n_active = (int32_t)nb;
+    if (small_sqp_direction_launch_x(ka, kp, 0, st) != 0) return fail(MIMGPU_ERR_CUDA, "k_sqp_direction_small_gj launch failed");
+    int rc = post_launch(c, "k_sqp_direction_small_gj");
+    if (rc) return rc;
+    if (dx) CU(cudaMemcpyAsync(dx + b0 * (T + 1) * nx, c->field[MIMGPU_F_DX] + b0 * (T + 1) * nx,
+                               nb * (T + 1) * nx * sizeof(double), cudaMemcpyDeviceToHost, st));
+    if (du) CU(cudaMemcpyAsync(du + b0 * T * nu, c->field[MIMGPU_F_DU] + b0 * T * nu, nb * T * nu * sizeof(double),
+                               cudaMemcpyDeviceToHost, st));
+    if (lag_mul) CU(cudaMemcpyAsync(lag_mul + b0 * (T + 1) * nx, c->field[MIMGPU_F_LAG_MUL] + b0 * (T + 1) * nx,
+                                    nb * (T + 1) * nx * sizeof(double), cudaMemcpyDeviceToHost, st));
+    if (kkt) CU(cudaMemcpyAsync(kkt + b0, c->k.scal + (size_t)MIMGPU_S_KKT * B + b0, nb * sizeof(double),
+                                cudaMemcpyDeviceToHost, st));
+  }
+  CU(cudaStreamSynchronize(c->pipe_st[0]));
+  CU(cudaStreamSynchronize(c->pipe_st[1]));
+  c->k.pack = c->pack_buf;
+  c->have_inputs = true;
+  c->extras_stale = true;
+  c->spill_packed = true;
+  c->last_sqp = kp;
+  return MIMGPU_OK;
 }
 
 int mimgpu_fddp_direction(mimgpu_ctx* c, const mimgpu_sqp_params* p, void* stream) {

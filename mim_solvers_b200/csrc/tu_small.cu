@@ -12,6 +12,8 @@ int small_sqp_direction_launch_x(const KArgs& a, const SqpKPar& kp, int variant,
 int small_pack_layout_x(const mimgpu_shape& s, size_t* pack_doubles, size_t* spill_doubles) {
   return small_pack_layout(s, pack_doubles, spill_doubles);
 }
-int small_pack_launch_x(const KArgs& a, double* pack, cudaStream_t st) { return small_pack_launch(a, pack, st); }
+int small_pack_launch_x(const KArgs& a, double* pack, int b0, int nb, cudaStream_t st) {
+  return small_pack_launch(a, pack, b0, nb, st);
+}
 int small_unpack_launch_x(const KArgs& a, cudaStream_t st) { return small_unpack_launch(a, st); }
 }  // namespace mimgpu

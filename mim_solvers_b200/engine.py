@@ -96,6 +96,17 @@ class BatchEngine:
             self.set_reg(preg, dreg)
         check(self._lib.mimgpu_sqp_direction(self._ctx, C.byref(p), self.stream), "mimgpu_sqp_direction")
 
+    def sqp_direction_host(self, batch: OCPBatch, params=None, *, dx=None, du=None, lag_mul=None, kkt=None,
+                           n_chunks: int = 8):
+        """Upload + computeDirection + download in overlapped slices (mimgpu_sqp_direction_host).
+        `batch` arrays and the output arrays should be pinned host memory; synchronous."""
+        p = params or _capi.default_sqp_params()
+        d = batch.derivs()
+        self._keep = batch
+        ptr = lambda a: None if a is None else a.ctypes.data
+        check(self._lib.mimgpu_sqp_direction_host(self._ctx, C.byref(d), C.byref(p), ptr(dx), ptr(du), ptr(lag_mul),
+                                                  ptr(kkt), int(n_chunks)), "mimgpu_sqp_direction_host")
+
     def fddp_direction(self, params=None):
         p = params or _capi.default_sqp_params()
         check(self._lib.mimgpu_fddp_direction(self._ctx, C.byref(p), self.stream), "mimgpu_fddp_direction")

@@ -28,7 +28,8 @@ _PTRS = ("Fx", "Fu", "Lxx", "Lxu", "Luu", "Lx", "Lu", "fs", "LxxT", "LxT",
 
 class KArgs(C.Structure):
     _fields_ = [("sh", _capi.Shape)] + [(n, C.c_void_p) for n in _PTRS] + [
-        ("n_active", C.c_int32), ("stage_fx", C.c_int32), ("pack", C.c_void_p), ("spill", C.c_void_p)]
+        ("n_active", C.c_int32), ("stage_fx", C.c_int32), ("pack", C.c_void_p), ("spill", C.c_void_p),
+        ("first", C.c_int32), ("pad_", C.c_int32)]
 
 
 def build(force=False):
