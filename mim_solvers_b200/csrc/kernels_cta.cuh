@@ -20,10 +20,10 @@ namespace mimgpu {
 template <int MODE>
 static __device__ __noinline__ int riccati_backward_ool(const Prob& p, double* sm, const Smem& s, const RicPar& rp,
                                                  int stage_fx) {
-  return riccati_backward<MODE>(p, sm, s, rp, stage_fx);
+  return riccati_backward<MODE>(p, as_shared(sm), s, rp, stage_fx);
 }
-static __device__ __noinline__ void csqp_forward_eq_ool(const Prob& p, double* sm, const Smem& s) { csqp_forward_eq(p, sm, s); }
-static __device__ __noinline__ void csqp_kkt_ool(const Prob& p, double* sm, const Smem& s) { csqp_kkt(p, sm, s); }
+static __device__ __noinline__ void csqp_forward_eq_ool(const Prob& p, double* sm, const Smem& s) { csqp_forward_eq(p, as_shared(sm), s); }
+static __device__ __noinline__ void csqp_kkt_ool(const Prob& p, double* sm, const Smem& s) { csqp_kkt(p, as_shared(sm), s); }
 
 struct StreamKPar {
   mimgpu_csqp_params q;
@@ -198,10 +198,10 @@ static inline int stream_csqp_launch(const KArgs& a, const mimgpu_csqp_params& q
 /* ============================================================ SQP / FDDP CTA kernels */
 
 static __device__ __noinline__ void sqp_forward_kkt_ool(const Prob& p, double* sm, const Smem& s, double mu, int stage_fx) {
-  sqp_forward_kkt(p, sm, s, mu, stage_fx);
+  sqp_forward_kkt(p, as_shared(sm), s, mu, stage_fx);
 }
 static __device__ __noinline__ void fddp_expected_improvement_ool(const Prob& p, double* sm, const Smem& s, int feas) {
-  fddp_expected_improvement(p, sm, s, feas);
+  fddp_expected_improvement(p, as_shared(sm), s, feas);
 }
 
 /* SolverSQP::computeDirection (src/sqp.cpp:224-242) / SolverFDDP::computeDirection +

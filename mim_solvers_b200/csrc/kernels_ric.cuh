@@ -145,6 +145,7 @@ template <int MODE, int NX, int NU>
 static __device__ __noinline__ int ric_backward_mma(const Prob& p, double* sm, const RicSmem& s, const RicPar& rp,
                                              uint64_t* bars, uint32_t& seq, bool eq_run = false) {
   using C = RicCfg<NX, NU>;
+  sm = as_shared(sm); /* keep LDS / STS addressing inside this out-of-line function */
   constexpr int N = C::N, XT = C::XT, NT = C::NT, KT = C::KT, UT = C::UT;
   constexpr bool FULL = (MODE == MODE_FULL), DDP = (MODE == MODE_DDP);
   /* eq_run: MODE_FULL code executing backwardPass_without_constraints (no constraint rows, no

@@ -60,7 +60,10 @@ __device__ __forceinline__ void tma_bulk_g2s(double* dst, const double* src, uin
  * shared window tells the address-space inference what it points to. */
 template <class T>
 __device__ __forceinline__ T* as_shared(T* p) {
-  return reinterpret_cast<T*>(__cvta_shared_to_generic(__cvta_generic_to_shared(const_cast<void*>(static_cast<const void*>(p)))));
+  extern __shared__ __align__(16) unsigned char mg_dyn_smem_base[]; /* aliases the kernel's dynamic array */
+  const unsigned off = (unsigned)__cvta_generic_to_shared(const_cast<void*>(static_cast<const void*>(p))) -
+                       (unsigned)__cvta_generic_to_shared(mg_dyn_smem_base);
+  return reinterpret_cast<T*>(mg_dyn_smem_base + off);
 }
 /* Ampere-style asynchronous copies for the small per-knot vectors (8 bytes per element) */
 __device__ __forceinline__ void cp_async8(double* smem_dst, const double* gsrc) {
@@ -599,6 +602,7 @@ struct SqpFwdSmem {
  * the knot's Fx, Fu, K, Vxx+ are streamed by TMA NS knots ahead, vectors through registers. */
 template <int NX, int NU, int SPLIT>
 static __device__ __noinline__ void stream_sqp_forward(const Prob& p, double* sm, PipeSqp<NX, NU>& pipe, double mu_dynamic) {
+  sm = as_shared(sm);
   using S = SqpFwdSmem<NX, NU>;
   constexpr int N = NX + NU, VPT = 3;
   const int T = p.T, tid = threadIdx.x, nth = blockDim.x, lane = tid & 31;
@@ -646,7 +650,7 @@ static __device__ __noinline__ void stream_sqp_forward(const Prob& p, double* sm
   const int grp = tid / SPLIT, q = tid % SPLIT, ngrp = nth / SPLIT;
   const int h = lane >> 4, l16 = lane & 15, w16 = (tid >> 5) * 16, n16 = (nth >> 5) * 16;
   for (int t = 0; t < T; ++t) {
-    const double* st = pipe.acquire();
+    const double* st = as_shared(pipe.acquire());
     const double *sFx = st, *sFu = st + NX * NX, *sK = st + NX * NX + NX * NU, *sV = sK + NX * NU;
     const double* x = sm + ((t & 1) ? S::x1 : S::x0);
     double* xn = sm + ((t & 1) ? S::x0 : S::x1);
