@@ -38,8 +38,12 @@ struct StreamKPar {
 template <int NX, int NU> struct StreamTune { static constexpr int MAXT = 256, MINB = 2; };
 template <> struct StreamTune<36, 12> { static constexpr int MAXT = 192, MINB = 2; };
 template <> struct StreamTune<32, 16> { static constexpr int MAXT = 192, MINB = 2; };
+/* DIRECT shapes: one CTA per SM (the Riccati layout of the full sweeps fills the shared memory) */
+template <> struct StreamTune<64, 32> { static constexpr int MAXT = 256, MINB = 1; };
+template <> struct StreamTune<76, 32> { static constexpr int MAXT = 256, MINB = 1; };
+template <> struct StreamTune<48, 24> { static constexpr int MAXT = 256, MINB = 1; };
 
-template <int NX, int NU, int SPLIT>
+template <int NX, int NU, int SPLIT, bool DIRECT = false>
 __global__ void __launch_bounds__(StreamTune<NX, NU>::MAXT, StreamTune<NX, NU>::MINB)
 k_csqp_direction_stream(KArgs a, StreamKPar kp) {
   static_assert(NX % 2 == 0 && NU % 2 == 0, "TMA bulk copies need 16-byte blocks");
@@ -51,7 +55,9 @@ k_csqp_direction_stream(KArgs a, StreamKPar kp) {
   double* sm = sm_stream;
   double* gsm = sm + ss.uni; /* generic Riccati layout lives in the union region */
   const Smem gs = smem_layout(NX, NU, p.ng, p.ngT, a.stage_fx);
-  constexpr bool USE_MMA = (NX % 4 == 0);
+  /* DIRECT shapes: the constrained DMMA Riccati layout does not fit the shared memory, their full
+   * sweeps run the shape-generic code */
+  constexpr bool USE_MMA = (NX % 4 == 0) && !DIRECT;
   const RicSmem rs = ric_layout<NX, NU>(p.ng, p.ngT, true);
   uint64_t* ric_bars = reinterpret_cast<uint64_t*>(sm + ss.bars) + 4;
   uint32_t ric_seq = 0u;
@@ -60,6 +66,7 @@ k_csqp_direction_stream(KArgs a, StreamKPar kp) {
   pipe.stages = sm + ss.uni;
   pipe.stage = ss.stage; pipe.ns = kp.ns; pipe.ng = p.ng;
   pipe.n_issue = 0; pipe.n_wait = 0; pipe.islot = 0; pipe.wslot = 0; pipe.wphase = 0u;
+  pipe.no_prefetch = (kp.dbg >> 3) & 1;
   if (threadIdx.x == 0) {
     for (int i = 0; i < kp.ns; ++i) mbar_init(pipe.bars + i, 1);
     mbar_init(ric_bars, 1);
@@ -100,11 +107,11 @@ k_csqp_direction_stream(KArgs a, StreamKPar kp) {
         if (st) break;
         fence_proxy_async(); /* K written through the generic proxy, read back by TMA */
       } else {
-        stream_backward_light<NX, NU, SPLIT>(p, sm, ss, pipe, q.sigma);
+        stream_backward_light<NX, NU, SPLIT, DIRECT>(p, sm, ss, pipe, q.sigma);
         stream_solve_gains<NU>(p);
       }
       __syncthreads();
-      stream_forward_update<NX, NU, SPLIT>(p, sm, ss, pipe, q, it, n);
+      stream_forward_update<NX, NU, SPLIT, DIRECT>(p, sm, ss, pipe, q, it, n);
       if (it % interval == 0) {
         const double scale = sqrt((n.primal * n.dual_rel) / (n.dual * n.primal_rel));
         const double rho_est = std_min(std_max(scale * rho_sparse, q.rho_min), q.rho_max);
@@ -173,10 +180,43 @@ static StreamPlan stream_plan_t(const mimgpu_shape& sh, int stage_fx, int max_sm
   return pl;
 }
 
+/* shapes whose knot does not fit two stages: no stage area, sweeps read global memory (L2-prefetched) */
+template <int NX, int NU, int SPLIT>
+static StreamPlan stream_plan_direct_t(const mimgpu_shape& sh, int stage_fx, int max_smem) {
+  StreamPlan pl{};
+  const Smem gs = smem_layout(NX, NU, sh.ng, sh.ngT, stage_fx);
+  pl.generic_total = gs.total;
+  const int ngm = sh.ng > sh.ngT ? sh.ng : sh.ngT;
+  int nt = SPLIT * (NX + NU);
+  if (2 * (NX + ngm) > nt) nt = 2 * (NX + ngm);
+  nt = ((nt + 31) / 32) * 32;
+  if (nt > StreamTune<NX, NU>::MAXT) nt = StreamTune<NX, NU>::MAXT;
+  pl.nt = nt;
+  const int nvmax = StreamCfg<NX, NU>::VPT * nt;
+  if (StreamCfg<NX, NU>::nv_bwd(sh.ng) > nvmax || StreamCfg<NX, NU>::nv_fwd(ngm) > nvmax) return pl;
+  const StreamSmem ss = stream_layout<NX, NU>(sh.ng, sh.ngT, 0, pl.generic_total);
+  const int bytes = ss.total * 8;
+  if (bytes > max_smem) return pl;
+  pl.ns = 0; pl.smem_bytes = bytes; pl.direct = 1;
+  if (cudaFuncSetAttribute(k_csqp_direction_stream<NX, NU, SPLIT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           bytes) != cudaSuccess) {
+    cudaGetLastError();
+    return pl;
+  }
+  pl.ok = 1;
+  return pl;
+}
+
+#define MIMGPU_DIRECT_SHAPES(X) X(64, 32, 4) X(76, 32, 4) X(48, 24, 4)
+
 static inline StreamPlan stream_plan(const mimgpu_shape& sh, int stage_fx, int max_smem) {
 #define X(NX_, NU_, SP_) \
   if (sh.nx == NX_ && sh.nu == NU_) return stream_plan_t<NX_, NU_, SP_>(sh, stage_fx, max_smem);
   MIMGPU_STREAM_SHAPES(X)
+#undef X
+#define X(NX_, NU_, SP_) \
+  if (sh.nx == NX_ && sh.nu == NU_) return stream_plan_direct_t<NX_, NU_, SP_>(sh, stage_fx, max_smem);
+  MIMGPU_DIRECT_SHAPES(X)
 #undef X
   return StreamPlan{};
 }
@@ -191,6 +231,13 @@ static inline int stream_csqp_launch(const KArgs& a, const mimgpu_csqp_params& q
     return 0;                                                                                         \
   }
   MIMGPU_STREAM_SHAPES(X)
+#undef X
+#define X(NX_, NU_, SP_)                                                                              \
+  if (a.sh.nx == NX_ && a.sh.nu == NU_) {                                                             \
+    k_csqp_direction_stream<NX_, NU_, SP_, true><<<a.n_active, pl.nt, pl.smem_bytes, st>>>(a, kp);    \
+    return 0;                                                                                         \
+  }
+  MIMGPU_DIRECT_SHAPES(X)
 #undef X
   return -1;
 }

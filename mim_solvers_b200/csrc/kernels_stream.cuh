@@ -74,6 +74,10 @@ template <int NPEND>
 __device__ __forceinline__ void cp_async_wait() {
   asm volatile("cp.async.wait_group %0;" ::"n"(NPEND) : "memory");
 }
+/* L2 prefetch of a contiguous global range (16-byte aligned, multiple of 16 bytes) */
+__device__ __forceinline__ void l2_prefetch(const double* src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
+}
 /* generic-proxy global writes (K, Quu_llt of a full sweep) -> later TMA reads of them */
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async;" ::: "memory"); }
 
@@ -124,6 +128,7 @@ struct Pipe {
   /* slot / phase of the next issue and of the next wait, advanced without integer division */
   int islot, wslot;
   uint32_t wphase;
+  int no_prefetch = 0; /* debug switch (MIMGPU_DBG bit 3) */
 
   /* The elected producer is lane 0 of the LAST warp: in the phases where the sweeps issue, that
    * warp has no outputs of its own (the mat-vec outputs are dealt to the first warps), so the
@@ -144,6 +149,21 @@ struct Pipe {
     }
     if (++islot == ns) islot = 0;
     ++n_issue;
+  }
+  /* DIRECT mode (shapes whose knot does not fit two shared-memory stages): the sweeps read the
+   * knot's matrices straight from global memory with coalesced accesses; the producer only pulls
+   * the knot into L2 a few knots ahead so that those reads are L2 hits. */
+  __device__ __forceinline__ void prefetch(const Prob& p, int t) {
+    if (threadIdx.x == blockDim.x - 32 && !no_prefetch) {
+      const size_t tt = (size_t)t;
+      l2_prefetch(p.Fx + tt * (NX * NX), NX * NX * 8);
+      l2_prefetch(p.Fu + tt * (NX * NU), NX * NU * 8);
+      l2_prefetch(p.K + tt * (NX * NU), NX * NU * 8);
+      if (ng) {
+        l2_prefetch(p.Gx + tt * (size_t)(ng * NX), (uint32_t)ng * NX * 8);
+        l2_prefetch(p.Gu + tt * (size_t)(ng * NU), (uint32_t)ng * NU * 8);
+      }
+    }
   }
   /* same, returning the slot index (callers that address the stage from the shared array itself) */
   __device__ __forceinline__ int acquire_slot() {
@@ -179,7 +199,7 @@ __device__ __forceinline__ double split_reduce(double v) {
 /* ------------------------------------------------------- light backward sweep */
 /* SolverCSQP::backwardPass_without_rho_update (src/csqp.cpp:1025-1108), gains deferred to
  * stream_solve_gains.  Writes Vx_, Qu_. */
-template <int NX, int NU, int SPLIT>
+template <int NX, int NU, int SPLIT, bool DIRECT = false>
 static __device__ __noinline__ void stream_backward_light(const Prob& p, double* sm, const StreamSmem& s, Pipe<NX, NU>& pipe,
                                       double sigma) {
   using C = StreamCfg<NX, NU>;
@@ -219,9 +239,15 @@ static __device__ __noinline__ void stream_backward_light(const Prob& p, double*
     }
     cp_async_commit();
   };
+  constexpr int PD = 3; /* DIRECT: L2 prefetch distance in knots */
   __syncthreads(); /* every stage and vector buffer is free */
-  for (int j = 0; j < pipe.ns - 1; ++j)
-    if (T - 1 - j >= 0) pipe.issue(p, T - 1 - j);
+  if (DIRECT) {
+    for (int j = 0; j < PD; ++j)
+      if (T - 1 - j >= 0) pipe.prefetch(p, T - 1 - j);
+  } else {
+    for (int j = 0; j < pipe.ns - 1; ++j)
+      if (T - 1 - j >= 0) pipe.issue(p, T - 1 - j);
+  }
   for (int j = 0; j < VD - 1; ++j) issue_pack(T - 1 - j);
   cp_async_wait<VD - 2>(); /* pack of knot T-1 has landed (made visible by the barrier below) */
   /* terminal knot (src/csqp.cpp:1045-1052) */
@@ -255,18 +281,23 @@ static __device__ __noinline__ void stream_backward_light(const Prob& p, double*
   }
   const int grp = tid / SPLIT, q = tid % SPLIT, ngrp = nth / SPLIT;
   for (int t = T - 1; t >= 0; --t) {
-    const double* st = sm + s.uni + pipe.acquire_slot() * s.stage;
+    const double* st = DIRECT ? nullptr : sm + s.uni + pipe.acquire_slot() * s.stage;
     __syncthreads(); /* A: tmp, d visible; knot t+1 completely consumed */
     issue_pack(t - (VD - 1));   /* into the slot of knot t+1, consumed before barrier A */
     cp_async_wait<VD - 2>();    /* this thread's share of pack t-1 has landed; barrier B publishes it */
     const double *sFx = st, *sFu = st + NX * NX, *sK = st + NX * NX + NX * NU, *sGx = sK + NX * NU,
                  *sGu = sGx + ng * NX;
+    if (DIRECT) {
+      sFx = p.Fx + (size_t)t * NX * NX; sFu = p.Fu + (size_t)t * NX * NU; sK = p.K + (size_t)t * NX * NU;
+      sGx = p.Gx + (size_t)t * ng * NX; sGu = p.Gu + (size_t)t * ng * NU;
+    }
     const double* v = vecof(t);
     /* P1: Qx, Qu (src/csqp.cpp:1068-1093) */
     for (int o0 = 0; o0 < NX + NU; o0 += ngrp) {
       const int o = o0 + grp;
-      const bool valid = o < NX + NU, isx = o < NX;
+      const bool valid = o < NX + NU;
       const int oc = valid ? o : 0;
+      const bool isx = oc < NX;   /* idle groups read column 0 of Fx: never a negative offset */
       const double* Fc = isx ? sFx + NX * oc : sFu + NX * (oc - NX);
       double acc = 0.0;
 #pragma unroll
@@ -301,7 +332,11 @@ static __device__ __noinline__ void stream_backward_light(const Prob& p, double*
     }
     __syncthreads(); /* B */
     /* refill the stage of knot t+1 (free since barrier A) while the last warp has no P2 rows */
-    if (t - (pipe.ns - 1) >= 0) pipe.issue(p, t - (pipe.ns - 1));
+    if (DIRECT) {
+      if (t - PD >= 0) pipe.prefetch(p, t - PD);
+    } else if (t - (pipe.ns - 1) >= 0) {
+      pipe.issue(p, t - (pipe.ns - 1));
+    }
     /* P2: Vx = Qx - K^T Qu (src/csqp.cpp:1101-1104); P0 of knot t-1 */
     for (int i = tid; i < NX; i += nth) {
       double acc = 0.0;
@@ -355,7 +390,7 @@ static __device__ __noinline__ void stream_solve_gains(const Prob& p) {
 /* ------------------------------------------------- forward pass + ADMM update */
 /* SolverCSQP::forwardPass (src/csqp.cpp:630-647) fused with update_lagrangian_parameters
  * (src/csqp.cpp:1196-1340): dx~, du~, z, y, dx_ := dx~, du_ := du~, residual norms. */
-template <int NX, int NU, int SPLIT>
+template <int NX, int NU, int SPLIT, bool DIRECT = false>
 static __device__ __noinline__ void stream_forward_update(const Prob& p, double* sm, const StreamSmem& s, Pipe<NX, NU>& pipe,
                                       const mimgpu_csqp_params& q_, int iter, AdmmNorms& n) {
   using C = StreamCfg<NX, NU>;
@@ -398,9 +433,15 @@ static __device__ __noinline__ void stream_forward_update(const Prob& p, double*
     }
     cp_async_commit();
   };
+  constexpr int PD = 3;
   __syncthreads();
-  for (int j = 0; j < pipe.ns - 1; ++j)
-    if (j < T) pipe.issue(p, j);
+  if (DIRECT) {
+    for (int j = 0; j < PD; ++j)
+      if (j < T) pipe.prefetch(p, j);
+  } else {
+    for (int j = 0; j < pipe.ns - 1; ++j)
+      if (j < T) pipe.issue(p, j);
+  }
   for (int j = 0; j < VD - 1; ++j) issue_pack(j);
   for (int i = tid; i < NX; i += nth) xs[0][i] = p.dxt[i];
   cp_async_wait<VD - 2>(); /* pack of knot 0 */
@@ -408,9 +449,13 @@ static __device__ __noinline__ void stream_forward_update(const Prob& p, double*
   const int grp = tid / SPLIT, q = tid % SPLIT, ngrp = nth / SPLIT;
   const int h = lane >> 4, l16 = lane & 15, w16 = (tid >> 5) * 16, n16 = (nth >> 5) * 16;
   for (int t = 0; t < T; ++t) {
-    const double* st = sm + s.uni + pipe.acquire_slot() * s.stage;
+    const double* st = DIRECT ? nullptr : sm + s.uni + pipe.acquire_slot() * s.stage;
     const double *sFx = st, *sFu = st + NX * NX, *sK = st + NX * NX + NX * NU, *sGx = sK + NX * NU,
                  *sGu = sGx + ng * NX;
+    if (DIRECT) {
+      sFx = p.Fx + (size_t)t * NX * NX; sFu = p.Fu + (size_t)t * NX * NU; sK = p.K + (size_t)t * NX * NU;
+      sGx = p.Gx + (size_t)t * ng * NX; sGu = p.Gu + (size_t)t * ng * NU;
+    }
     const double* x = xs[t & 1];
     double* xn = xs[(t + 1) & 1];
     const double* v = vecof(t);
@@ -436,7 +481,11 @@ static __device__ __noinline__ void stream_forward_update(const Prob& p, double*
     }
     for (int i = tid; i < NX; i += nth) p.dx[(size_t)t * NX + i] = x[i];
     __syncthreads(); /* 1: du~ visible; knot t-1 completely consumed */
-    if (t + pipe.ns - 1 < T) pipe.issue(p, t + pipe.ns - 1);
+    if (DIRECT) {
+      if (t + PD < T) pipe.prefetch(p, t + PD);
+    } else if (t + pipe.ns - 1 < T) {
+      pipe.issue(p, t + pipe.ns - 1);
+    }
     issue_pack(t + VD - 1);   /* into the slot of knot t-1 */
     cp_async_wait<VD - 2>();  /* this thread's share of pack t+1 has landed; barrier 2 publishes it */
     /* F2: dx~+ = fs+ + Fx dx~ + Fu du~ (src/csqp.cpp:638-644) and the constraint rows of knot t
@@ -444,8 +493,9 @@ static __device__ __noinline__ void stream_forward_update(const Prob& p, double*
      * two half-warps share one output (even / odd contraction index) */
     for (int o0 = 0; o0 < NX + ng; o0 += n16) {
       const int o = o0 + w16 + l16;
-      const bool valid = o < NX + ng, isx = o < NX;
+      const bool valid = o < NX + ng;
       const int oc = valid ? o : 0;
+      const bool isx = oc < NX;   /* idle lanes read row 0 of Fx: never a negative offset */
       const int ld = isx ? NX : ng, row = isx ? oc : oc - NX;
       const double* A1 = (isx ? sFx : sGx) + row;
       const double* A2 = (isx ? sFu : sGu) + row;

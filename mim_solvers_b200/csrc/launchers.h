@@ -11,7 +11,7 @@
 namespace mimgpu {
 
 struct StreamPlan {
-  int ok, ns, nt, smem_bytes, generic_total;
+  int ok, ns, nt, smem_bytes, generic_total, direct;
 };
 struct CtaPlan {
   int ok, nt, smem_bytes, nbuf, ns;

@@ -68,6 +68,26 @@ def test_gpu_csqp_vs_oracle(eng, oracle_lib, B, T, nx, nu, ng, ngT, kw):
     compare_engines_csqp(lambda b: eng(b), lambda b: oracle_lib.Oracle(b), batch, params=p, n_calls=2)
 
 
+@pytest.mark.parametrize("B,T,nx,nu,ng,ngT", [(16, 12, 76, 32, 32, 0), (8, 9, 48, 24, 30, 20), (16, 12, 36, 12, 16, 0)])
+def test_gpu_csqp_device_attached_separate_allocations(oracle_lib, B, T, nx, nu, ng, ngT):
+    """Each derivative array in its own cudaMalloc block (the caller-owned layout of the drop-in): an index one
+    element outside an array faults here instead of landing in a neighbouring array of the engine's single upload
+    buffer.  Covers the streaming kernel in staged and in direct (L2-prefetch) mode."""
+    import torch
+    from mim_solvers_b200 import _capi
+    from mim_solvers_b200.engine import BatchEngine
+    from mim_solvers_b200.problems import make_random_batch
+    batch = make_random_batch(B, T, nx, nu, ng=ng, ngT=ngT, box_rows=min(ng, nx))
+    p = _capi.default_csqp_params(max_qp_iters=40)
+
+    def mk(b):
+        e = BatchEngine(shape=b.shape())
+        e._keepalive = {k: torch.from_numpy(v).cuda() for k, v in b.arrays.items()}
+        e.attach_device(e._keepalive)
+        return e
+    compare_engines_csqp(mk, lambda b: oracle_lib.Oracle(b), batch, params=p, n_calls=2)
+
+
 def test_gpu_csqp_benchmark_protocol(eng, oracle_lib):
     """benchmarks/solo12.cpp:213-216: eps_abs = eps_rel = 0, 50 iterations, no eq. guess."""
     from mim_solvers_b200 import _capi
