@@ -478,34 +478,40 @@ class SolverFDDP(_SolverBase):
         self.KKT = np.maximum(k, np.abs(self.fs).max(axis=(1, 2)))
         return self.KKT
 
-    def forwardPass(self, steplength):
-        """src/fddp.cpp:281-383: nonlinear roll-out with the feedback gains."""
+    def forwardPass(self, steplength, mask=None):
+        """src/fddp.cpp:281-383: nonlinear roll-out with the feedback gains.  Only the problems of
+        `mask` commit their members (lag_mul_, dx_, xs_try_, us_try_, fs_try_): a problem that has
+        already accepted a step must not be rolled again by its neighbours' smaller alphas."""
         p, T = self.problem, self.T
+        m = np.ones(self.B, dtype=bool) if mask is None else mask
         K, kff = self._K_cache, self._k_cache
         Vxx = np.swapaxes(self._Vxx_cache, -1, -2)
         closed = self.is_feasible or steplength == 1
         xnext = p.x0.copy()
         cost = np.zeros(self.B)
         gap = np.zeros(self.B)
-        dxs = self._dx_roll
+        dxs, lag = self._dx_roll.copy(), self._lag_mul.copy()
+        xs_try, us_try, fs_try_all = self.xs_try.copy(), self.us_try.copy(), self.fs_try.copy()
         bad = np.zeros(self.B, dtype=bool)
         for t in range(T):
             shift = dxs[:, t] if closed else dxs[:, t] - self.fs[:, t]
-            self._lag_mul[:, t] = np.einsum("bij,bj->bi", Vxx[:, t], shift) + self._Vx_cache[:, t]
-            self.xs_try[:, t] = xnext if closed else p.integrate(xnext, self.fs[:, t] * (steplength - 1))
-            dxs[:, t] = p.diff(self.xs[:, t], self.xs_try[:, t])
-            self.us_try[:, t] = self.us[:, t] - kff[:, t] * steplength - np.einsum("bij,bj->bi", K[:, t], dxs[:, t])
-            xnext, c = p.calc_knot(t, self.xs_try[:, t], self.us_try[:, t])
+            lag[:, t] = np.einsum("bij,bj->bi", Vxx[:, t], shift) + self._Vx_cache[:, t]
+            xs_try[:, t] = xnext if closed else p.integrate(xnext, self.fs[:, t] * (steplength - 1))
+            dxs[:, t] = p.diff(self.xs[:, t], xs_try[:, t])
+            us_try[:, t] = self.us[:, t] - kff[:, t] * steplength - np.einsum("bij,bj->bi", K[:, t], dxs[:, t])
+            xnext, c = p.calc_knot(t, xs_try[:, t], us_try[:, t])
             cost += c
-            fs_try = p.diff(self.xs_try[:, t], xnext)
-            self.fs_try[:, t] = fs_try
+            fs_try = p.diff(xs_try[:, t], xnext)
+            fs_try_all[:, t] = fs_try
             gap += np.abs(fs_try).sum(axis=1)
             bad |= _raise_if_nan(cost) | _raise_if_nan(np.abs(xnext).max(axis=1))
         shift = dxs[:, T] if closed else dxs[:, T] - self.fs[:, T]
-        self._lag_mul[:, T] = np.einsum("bij,bj->bi", Vxx[:, T], shift) + self._Vx_cache[:, T]
-        self.xs_try[:, T] = xnext if closed else p.integrate(xnext, self.fs[:, T] * (steplength - 1))
-        cost += p.calc_terminal(self.xs_try[:, T])
+        lag[:, T] = np.einsum("bij,bj->bi", Vxx[:, T], shift) + self._Vx_cache[:, T]
+        xs_try[:, T] = xnext if closed else p.integrate(xnext, self.fs[:, T] * (steplength - 1))
+        cost += p.calc_terminal(xs_try[:, T])
         bad |= _raise_if_nan(cost)
+        self._dx_roll[m], self._lag_mul[m] = dxs[m], lag[m]
+        self.xs_try[m], self.us_try[m], self.fs_try[m] = xs_try[m], us_try[m], fs_try_all[m]
         return cost, gap, bad
 
     def solve(self, init_xs=None, init_us=None, maxiter=100, is_feasible=False, reginit=float("nan")):
@@ -548,8 +554,8 @@ class SolverFDDP(_SolverBase):
                 if not searching.any():
                     break
                 self.steplength[searching] = alpha
-                cost_try, gap_try, bad = self.forwardPass(alpha)
-                self.cost_try, self.gap_norm_try = cost_try, gap_try
+                cost_try, gap_try, bad = self.forwardPass(alpha, searching)
+                self.cost_try[searching], self.gap_norm_try[searching] = cost_try[searching], gap_try[searching]
                 self.dV = self.cost - cost_try
                 if self.use_filter_line_search:
                     ok = self._filter_accepts((costs, gaps), (cost_try, gap_try), self.iter)

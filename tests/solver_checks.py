@@ -99,7 +99,9 @@ def check_fddp_lq(factory):
     s = SolverFDDP(p, factory)
     ok = s.solve(maxiter=10)
     assert ok.all(), (s.KKT, s.iter)
-    assert (s.iter <= 2).all(), s.iter
+    # one Newton step reaches the optimum; lag_mul_ (hence KKT_) is refreshed by the NEXT roll-out
+    # (src/fddp.cpp:302,343), so the reference needs up to two more iterations to see it
+    assert (s.iter <= 3).all(), s.iter
     ref = SolverSQP(p, factory)
     ref.solve(maxiter=10)
     assert np.abs(ref.us - s.us).max() < 1e-5
