@@ -36,7 +36,14 @@ struct StreamKPar {
  * forward/update sweep replaced by the streaming versions above. */
 /* CTA size cap and resident CTAs per SM (register budget) per shape */
 template <int NX, int NU> struct StreamTune { static constexpr int MAXT = 256, MINB = 2; };
-template <> struct StreamTune<36, 12> { static constexpr int MAXT = 192, MINB = 2; };
+#ifndef MIMGPU_TUNE_C3_MINB
+#define MIMGPU_TUNE_C3_MINB 3
+#endif
+#ifndef MIMGPU_TUNE_C1_MINB
+#define MIMGPU_TUNE_C1_MINB 8
+#endif
+template <> struct StreamTune<36, 12> { static constexpr int MAXT = 192, MINB = MIMGPU_TUNE_C3_MINB; };
+template <> struct StreamTune<12, 6> { static constexpr int MAXT = 96, MINB = MIMGPU_TUNE_C1_MINB; };
 template <> struct StreamTune<32, 16> { static constexpr int MAXT = 192, MINB = 2; };
 /* DIRECT shapes: one CTA per SM (the Riccati layout of the full sweeps fills the shared memory) */
 template <> struct StreamTune<64, 32> { static constexpr int MAXT = 256, MINB = 1; };
@@ -164,10 +171,10 @@ static StreamPlan stream_plan_t(const mimgpu_shape& sh, int stage_fx, int max_sm
   if (StreamCfg<NX, NU>::nv_bwd(sh.ng) > nvmax || StreamCfg<NX, NU>::nv_fwd(ngm) > nvmax) return pl;
   for (int ns = 3; ns >= 2; --ns) {
     const StreamSmem ss = stream_layout<NX, NU>(sh.ng, sh.ngT, ns, pl.generic_total);
-    /* more than two stages only while at least two CTAs still fit an SM */
+    /* more than two stages only while the shape's target of resident CTAs still fits an SM */
     const int bytes = ss.total * 8;
     if (bytes > max_smem) continue;
-    if (ns >= 3 && 2 * (bytes + 1024) > 233472) continue;
+    if (ns >= 3 && StreamTune<NX, NU>::MINB * (bytes + 1024) > 233472) continue;
     pl.ns = ns; pl.smem_bytes = bytes;
     if (cudaFuncSetAttribute(k_csqp_direction_stream<NX, NU, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              bytes) != cudaSuccess) {

@@ -180,6 +180,33 @@ __device__ __forceinline__ int small_backward_gj(const double* pk, double* sp, i
     spill_value(T);
   }
 
+  /* Per-lane table of where each element of the M fragments sits in a staged input record
+   * (knot-invariant): 10-bit offsets packed three to a word, one validity bit per element.
+   * Element (i, n) of [[Lxx Lxu | Lx], [Lxu^T Luu | Lu]]: rows / columns >= N (+1) are padding. */
+  static_assert(C::REC < 1024, "10-bit record offsets");
+  static_assert(NT * NTC * 2 <= 32, "one validity bit per fragment element");
+  uint32_t hoff[(NT * NTC * 2 + 2) / 3];
+  uint32_t hmask = 0;
+#pragma unroll
+  for (int w = 0; w < (NT * NTC * 2 + 2) / 3; ++w) hoff[w] = 0;
+#pragma unroll
+  for (int it = 0; it < NT; ++it)
+#pragma unroll
+    for (int nt = 0; nt < NTC; ++nt)
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const int k = (it * NTC + nt) * 2 + e;
+        const int i = 8 * it + g, n = 8 * nt + 2 * tq + e;
+        int off = 0;
+        bool valid = false;
+        if (i < NX && n < N) { off = C::bH + i + NX * n; valid = true; }                              /* Lxx | Lxu */
+        else if (i < N && n < NX) { off = C::bH + n + NX * i; valid = true; }                        /* Lxu^T */
+        else if (i < N && n < N) { off = C::bLuu + (i - NX) + NU * (n - NX); valid = true; }         /* Luu */
+        else if (i < N && n == N) { off = C::bL + i; valid = true; }                                 /* Lx | Lu */
+        hoff[k / 3] |= (uint32_t)off << (10 * (k % 3));
+        hmask |= (valid ? 1u : 0u) << k;
+      }
+
   for (int t = T - 1; t >= 0; --t) {
     const int j = T - 1 - t, s = j & 1;          /* load sequence number -> stage, mbarrier phase */
     double* st = sw + (s ? C::oS1 : C::oS0);
@@ -224,7 +251,8 @@ __device__ __forceinline__ int small_backward_gj(const double* pk, double* sp, i
         for (int nt = 0; nt < NT; ++nt) dmma884(wt[nt][kp][0], wt[nt][kp][1], fa[nt][kt], vb);
       }
     }
-    /* ---- M = [H | l]: Lxx Lxu / Lxu^T Luu (+ dreg), gradient column = [Lx; Lu] + F^T Vx' */
+    /* ---- M = [H | l]: Lxx Lxu / Lxu^T Luu (+ dreg), gradient column = [Lx; Lu] + F^T Vx'.
+     * One predicated load per element through the lane's packed offset table (no divergence). */
 #pragma unroll
     for (int it = 0; it < NT; ++it) {
       const int i = 8 * it + g;
@@ -233,14 +261,12 @@ __device__ __forceinline__ int small_backward_gj(const double* pk, double* sp, i
       for (int nt = 0; nt < NTC; ++nt)
 #pragma unroll
         for (int e = 0; e < 2; ++e) {
+          const int k = (it * NTC + nt) * 2 + e;
           const int n = 8 * nt + 2 * tq + e;
-          double v = 0.0;
-          if (i < NX && n < N) v = st[C::bH + i + NX * n];                          /* Lxx | Lxu */
-          else if (i < N && n < NX) v = st[C::bH + n + NX * i];                     /* Lxu^T */
-          else if (i < N && n < N) {
-            v = st[C::bLuu + (i - NX) + NU * (n - NX)];                             /* Luu (+ dreg) */
-            if (i == n && use_dreg) v += dreg;
-          } else if (i < N && n == N) v = st[C::bL + i] + qv;                       /* Qx | Qu */
+          const int off = (int)((hoff[k / 3] >> (10 * (k % 3))) & 1023u);
+          double v = ((hmask >> k) & 1u) ? st[off] : 0.0;
+          if (it == nt && it >= NX / 8 && use_dreg && i == n && i >= NX && i < N) v += dreg;   /* Luu + dreg */
+          if (nt == RCT && n == N && i < N) v += qv;                                           /* Qx | Qu */
           m[it][nt][e] = v;
         }
     }
