@@ -8,6 +8,8 @@
  *   k_fddp_direction_cta     SolverFDDP::computeDirection (src/fddp.cpp:189-204)
  */
 #pragma once
+#include <cstdio>
+#include <cstdlib>
 #include "launchers.h"
 #include "kernels_ric.cuh"
 #include "kernels_stream.cuh"
@@ -35,9 +37,11 @@ struct StreamKPar {
  * csqp_direction_body (kernels_generic.cuh) with the light sweep, the gain solve and the
  * forward/update sweep replaced by the streaming versions above. */
 /* CTA size cap and resident CTAs per SM (register budget) per shape */
-template <int NX, int NU> struct StreamTune { static constexpr int MAXT = 256, MINB = 2; };
+template <int NX, int NU> struct StreamTune {
+  static constexpr int MAXT = NX <= 16 ? 128 : 256, MINB = NX <= 16 ? 6 : 2;
+};
 #ifndef MIMGPU_TUNE_C3_MINB
-#define MIMGPU_TUNE_C3_MINB 3
+#define MIMGPU_TUNE_C3_MINB 2
 #endif
 #ifndef MIMGPU_TUNE_C1_MINB
 #define MIMGPU_TUNE_C1_MINB 8
@@ -262,12 +266,13 @@ static __device__ __noinline__ void fddp_expected_improvement_ool(const Prob& p,
  * updateExpectedImprovement (src/fddp.cpp:189-204, 256-279): DMMA backward sweep, then the
  * shape-generic forward pass / KKT (SQP) or expected-improvement reductions (FDDP). */
 template <int NX, int NU>
-struct CtaTune { /* 4 lanes per right-hand side of the gain solve */
+struct CtaTune { /* 4 lanes per right-hand side of the gain solve; MINB = resident CTAs per SM aimed at */
   static constexpr int MAXT = ((4 * (NX + 1) + 31) / 32) * 32 > 512 ? 512 : ((4 * (NX + 1) + 31) / 32) * 32;
+  static constexpr int MINB = NX <= 16 ? 6 : NX <= 24 ? 4 : NX <= 36 ? 3 : 1;
 };
 
 template <int NX, int NU, bool FDDP>
-__global__ void __launch_bounds__(CtaTune<NX, NU>::MAXT, 1) k_sqp_direction_cta(KArgs a, SqpKPar kp, int nbuf, int ns) {
+__global__ void __launch_bounds__(CtaTune<NX, NU>::MAXT, CtaTune<NX, NU>::MINB) k_sqp_direction_cta(KArgs a, SqpKPar kp, int nbuf, int ns) {
   extern __shared__ __align__(16) double sm_cta[];
   if ((int)blockIdx.x >= a.n_active) return;
   const int b = a.active ? a.active[blockIdx.x] : (int)blockIdx.x;
@@ -326,26 +331,34 @@ static CtaPlan cta_plan_t(const mimgpu_shape& sh, int stage_fx, int max_smem) {
   CtaPlan pl{};
   const Smem gs = smem_layout(NX, NU, 0, 0, stage_fx);
   pl.nt = CtaTune<NX, NU>::MAXT;
-  for (int nbuf = 2; nbuf >= 1; --nbuf) {
-    const RicSmem rs = ric_layout<NX, NU>(0, 0, false, nbuf);
-    int tot = rs.total > gs.total ? rs.total : gs.total;
-    if ((8 + tot) * 8 > max_smem) continue;
-    /* streaming forward pass: 3 or 2 stages next to its vectors, inside the same union */
-    pl.ns = 0;
-    for (int ns = 3; ns >= 2; --ns) {
-      const int f = SqpFwdSmem<NX, NU>::stages + ns * PipeSqp<NX, NU>::STAGE;
-      if ((8 + f) * 8 <= max_smem) { pl.ns = ns; if (f > tot) tot = f; break; }
-    }
-    pl.nbuf = nbuf; pl.smem_bytes = (8 + tot) * 8;
-    if (cudaFuncSetAttribute(k_sqp_direction_cta<NX, NU, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             pl.smem_bytes) != cudaSuccess ||
-        cudaFuncSetAttribute(k_sqp_direction_cta<NX, NU, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             pl.smem_bytes) != cudaSuccess) {
-      cudaGetLastError();
+  /* first pass: the largest staging that still lets MINB CTAs share an SM; second pass: whatever fits */
+  const int budget = 233472 / CtaTune<NX, NU>::MINB - 1024;
+  for (int pass = 0; pass < 2; ++pass) {
+    const int limit = (pass == 0 && budget < max_smem) ? budget : max_smem;
+    for (int nbuf = 2; nbuf >= 1; --nbuf) {
+      const RicSmem rs = ric_layout<NX, NU>(0, 0, false, nbuf);
+      int tot = rs.total > gs.total ? rs.total : gs.total;
+      if ((8 + tot) * 8 > limit) continue;
+      /* streaming forward pass: 3 or 2 stages next to its vectors, inside the same union */
+      pl.ns = 0;
+      for (int ns = 3; ns >= 2; --ns) {
+        const int f = SqpFwdSmem<NX, NU>::stages + ns * PipeSqp<NX, NU>::STAGE;
+        if ((8 + f) * 8 <= limit) { pl.ns = ns; if (f > tot) tot = f; break; }
+      }
+      pl.nbuf = nbuf; pl.smem_bytes = (8 + tot) * 8;
+      if (getenv("MIMGPU_DBG_PLAN"))
+        fprintf(stderr, "cta_plan<%d,%d>: nt %d nbuf %d ns %d smem %d B (pass %d, MINB %d)\n", NX, NU, pl.nt, pl.nbuf,
+                pl.ns, pl.smem_bytes, pass, CtaTune<NX, NU>::MINB);
+      if (cudaFuncSetAttribute(k_sqp_direction_cta<NX, NU, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               pl.smem_bytes) != cudaSuccess ||
+          cudaFuncSetAttribute(k_sqp_direction_cta<NX, NU, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               pl.smem_bytes) != cudaSuccess) {
+        cudaGetLastError();
+        return pl;
+      }
+      pl.ok = 1;
       return pl;
     }
-    pl.ok = 1;
-    return pl;
   }
   return pl;
 }

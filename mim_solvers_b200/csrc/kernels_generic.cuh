@@ -214,6 +214,63 @@ MG_DEV void llt_solve_multi(const double* L, int n, double* b, int nrhs, int inc
   }
 }
 
+/* C(i, j) = sum_k A[k + lda * i] * B[k + ldb * j]  (i < ni, j < nj), handed to store(i, j, sum).
+ * Each thread owns the four elements (i | i + hi) x (j | j + hj): two loads feed two FMAs instead
+ * of one, and lanes still walk consecutive i (same bank pattern as one element per thread).
+ * Every element keeps its own k-ascending sum, so results are bit-identical to the plain loop. */
+template <class Store>
+MG_DEV void tiled_tn(const double* A, int lda, int ni, const double* B, int ldb, int nj, int nk, Store store) {
+  const int hi = (ni + 1) / 2, hj = (nj + 1) / 2;
+  MG_PAR(te, hi * hj) {
+    const int i0 = te % hi, j0 = te / hi, i1 = i0 + hi, j1 = j0 + hj;
+    const bool ri = i1 < ni, rj = j1 < nj;
+    const double *a0 = A + (size_t)lda * i0, *a1 = A + (size_t)lda * (ri ? i1 : i0);
+    const double *b0 = B + (size_t)ldb * j0, *b1 = B + (size_t)ldb * (rj ? j1 : j0);
+    double c00 = 0.0, c10 = 0.0, c01 = 0.0, c11 = 0.0;
+    for (int k = 0; k < nk; ++k) {
+      const double x0 = a0[k], x1 = a1[k], y0 = b0[k], y1 = b1[k];
+      c00 += x0 * y0; c10 += x1 * y0; c01 += x0 * y1; c11 += x1 * y1;
+    }
+    store(i0, j0, c00);
+    if (ri) store(i1, j0, c10);
+    if (rj) store(i0, j1, c01);
+    if (ri && rj) store(i1, j1, c11);
+  }
+}
+
+/* C(i, j) = base(i, j) + [sum_r G[r + ng * i] * (rho[r] * H[r + ng * j])] + sum_k A[i + lda * k] * B[k + ldb * j]
+ * with the same 2 x 2 ownership; the bracket is skipped when G is null.  finish(i, j, gsum, sum)
+ * combines and stores.  Summation orders per element are those of the plain loops. */
+template <class Finish>
+MG_DEV void tiled_nn_g(const double* A, int lda, int ni, const double* B, int ldb, int nj, int nk,
+                       const double* G, const double* H, const double* rho, int ng, Finish finish) {
+  const int hi = (ni + 1) / 2, hj = (nj + 1) / 2;
+  MG_PAR(te, hi * hj) {
+    const int i0 = te % hi, j0 = te / hi, i1 = i0 + hi, j1 = j0 + hj;
+    const bool ri = i1 < ni, rj = j1 < nj;
+    const int i1c = ri ? i1 : i0, j1c = rj ? j1 : j0;
+    double g00 = 0.0, g10 = 0.0, g01 = 0.0, g11 = 0.0;
+    if (G) {
+      const double *p0 = G + (size_t)ng * i0, *p1 = G + (size_t)ng * i1c;
+      const double *q0 = H + (size_t)ng * j0, *q1 = H + (size_t)ng * j1c;
+      for (int r = 0; r < ng; ++r) {
+        const double x0 = p0[r], x1 = p1[r], y0 = rho[r] * q0[r], y1 = rho[r] * q1[r];
+        g00 += x0 * y0; g10 += x1 * y0; g01 += x0 * y1; g11 += x1 * y1;
+      }
+    }
+    const double *b0 = B + (size_t)ldb * j0, *b1 = B + (size_t)ldb * j1c;
+    double c00 = 0.0, c10 = 0.0, c01 = 0.0, c11 = 0.0;
+    for (int k = 0; k < nk; ++k) {
+      const double x0 = A[i0 + (size_t)lda * k], x1 = A[i1c + (size_t)lda * k], y0 = b0[k], y1 = b1[k];
+      c00 += x0 * y0; c10 += x1 * y0; c01 += x0 * y1; c11 += x1 * y1;
+    }
+    finish(i0, j0, g00, c00);
+    if (ri) finish(i1, j0, g10, c10);
+    if (rj) finish(i0, j1, g01, c01);
+    if (ri && rj) finish(i1, j1, g11, c11);
+  }
+}
+
 /* One right-hand side, column-oriented so that the CTA shares the work; every x[i]
  * still subtracts its terms in the reference's order (j ascending / descending). */
 MG_DEV void llt_solve_one(const double* L, int n, double* x) {
@@ -344,18 +401,8 @@ MG_DEV int riccati_backward(const Prob& p, double* sm, const Smem& s, const RicP
       MG_SYNC();
     }
     /* ---- phase A: FxTVxx, FuTVxx, Qx, Qu  (src/ddp.cpp:289-302) */
-    MG_PAR(e, nxx) {
-      const int i = e % nx, j = e / nx;
-      double acc = 0.0;
-      for (int k = 0; k < nx; ++k) acc += Fx[k + lfx * i] * V[k + nx * j];
-      W[e] = acc;
-    }
-    MG_PAR(e, nxu) {
-      const int a = e % nu, j = e / nu;
-      double acc = 0.0;
-      for (int k = 0; k < nx; ++k) acc += Fu[k + ldx * a] * V[k + nx * j];
-      FuTV[e] = acc;
-    }
+    tiled_tn(Fx, lfx, nx, V, nx, nx, nx, [&](int i, int j, double acc) { W[i + nx * j] = acc; });
+    tiled_tn(Fu, ldx, nu, V, nx, nx, nx, [&](int a, int j, double acc) { FuTV[a + nu * j] = acc; });
     MG_PAR(i, nx) {
       double v = p.Lx[(size_t)t * nx + i];
       if (MODE == MODE_FULL) {
@@ -386,20 +433,17 @@ MG_DEV int riccati_backward(const Prob& p, double* sm, const Smem& s, const RicP
     }
     MG_SYNC();
     /* ---- phase B: Qxx (into V), Quu, Qxu  (src/ddp.cpp:295-314, src/csqp.cpp:743-780) */
-    MG_PAR(e, nxx) {
-      const int i = e % nx, j = e / nx;
-      double v = p.Lxx[(size_t)t * nxx + e];
-      if (MODE == MODE_FULL) {
-        if (i == j) v += sigma;
-        if (gx_on) {
-          double acc = 0.0;
-          for (int r = 0; r < ng; ++r) acc += Gx[r + ng * i] * (srho[r] * Gx[r + ng * j]);
-          v += acc;
-        }
-      }
-      double acc = 0.0;
-      for (int k = 0; k < nx; ++k) acc += W[i + nx * k] * Fx[k + lfx * j];
-      V[e] = v + acc;
+    {
+      const double* lxx = p.Lxx + (size_t)t * nxx;
+      tiled_nn_g(W, nx, nx, Fx, lfx, nx, nx, gx_on ? Gx : nullptr, Gx, srho, ng,
+                 [&](int i, int j, double gacc, double acc) {
+                   double v = lxx[i + nx * j];
+                   if (MODE == MODE_FULL) {
+                     if (i == j) v += sigma;
+                     if (gx_on) v += gacc;
+                   }
+                   V[i + nx * j] = v + acc;
+                 });
     }
     MG_PAR(e, nuu) {
       const int a = e % nu, c = e / nu;
@@ -417,17 +461,14 @@ MG_DEV int riccati_backward(const Prob& p, double* sm, const Smem& s, const RicP
       Quu[e] = v;
       L[e] = v;
     }
-    MG_PAR(e, nxu) {
-      const int i = e % nx, a = e / nx;
-      double v = p.Lxu[(size_t)t * nxu + e];
-      if (gx_on) {
-        double acc = 0.0;
-        for (int r = 0; r < ng; ++r) acc += Gx[r + ng * i] * (srho[r] * Gu[r + ng * a]);
-        v += acc;
-      }
-      double acc = 0.0;
-      for (int k = 0; k < nx; ++k) acc += W[i + nx * k] * Fu[k + ldx * a];
-      Qxu[e] = v + acc;
+    {
+      const double* lxu = p.Lxu + (size_t)t * nxu;
+      tiled_nn_g(W, nx, nx, Fu, ldx, nu, nx, gx_on ? Gx : nullptr, Gu, srho, ng,
+                 [&](int i, int a, double gacc, double acc) {
+                   double v = lxu[i + nx * a];
+                   if (gx_on) v += gacc;
+                   Qxu[i + nx * a] = v + acc;
+                 });
     }
     MG_SYNC();
     /* ---- computeGains (src/ddp.cpp:401-429) */
