@@ -215,59 +215,76 @@ MG_DEV void llt_solve_multi(const double* L, int n, double* b, int nrhs, int inc
 }
 
 /* C(i, j) = sum_k A[k + lda * i] * B[k + ldb * j]  (i < ni, j < nj), handed to store(i, j, sum).
- * Each thread owns the four elements (i | i + hi) x (j | j + hj): two loads feed two FMAs instead
- * of one, and lanes still walk consecutive i (same bank pattern as one element per thread).
- * Every element keeps its own k-ascending sum, so results are bit-identical to the plain loop. */
+ * Each thread owns the 2 x 4 elements (i | i + hi) x (j + q hj, q < 4): six loads feed eight FMAs
+ * instead of two feeding one, lanes still walk consecutive i (same bank pattern as one element per
+ * thread) and the B operands are warp broadcasts.  Every element keeps its own k-ascending sum,
+ * so results are bit-identical to the plain loop. */
+#define MG_TJ 4
 template <class Store>
 MG_DEV void tiled_tn(const double* A, int lda, int ni, const double* B, int ldb, int nj, int nk, Store store) {
-  const int hi = (ni + 1) / 2, hj = (nj + 1) / 2;
+  const int hi = (ni + 1) / 2, hj = (nj + MG_TJ - 1) / MG_TJ;
   MG_PAR(te, hi * hj) {
-    const int i0 = te % hi, j0 = te / hi, i1 = i0 + hi, j1 = j0 + hj;
-    const bool ri = i1 < ni, rj = j1 < nj;
+    const int i0 = te % hi, j0 = te / hi, i1 = i0 + hi;
+    const bool ri = i1 < ni;
     const double *a0 = A + (size_t)lda * i0, *a1 = A + (size_t)lda * (ri ? i1 : i0);
-    const double *b0 = B + (size_t)ldb * j0, *b1 = B + (size_t)ldb * (rj ? j1 : j0);
-    double c00 = 0.0, c10 = 0.0, c01 = 0.0, c11 = 0.0;
-    for (int k = 0; k < nk; ++k) {
-      const double x0 = a0[k], x1 = a1[k], y0 = b0[k], y1 = b1[k];
-      c00 += x0 * y0; c10 += x1 * y0; c01 += x0 * y1; c11 += x1 * y1;
+    const double* b[MG_TJ];
+    double c0[MG_TJ], c1[MG_TJ];
+#pragma unroll
+    for (int q = 0; q < MG_TJ; ++q) {
+      const int j = j0 + q * hj;
+      b[q] = B + (size_t)ldb * (j < nj ? j : j0);
+      c0[q] = 0.0; c1[q] = 0.0;
     }
-    store(i0, j0, c00);
-    if (ri) store(i1, j0, c10);
-    if (rj) store(i0, j1, c01);
-    if (ri && rj) store(i1, j1, c11);
+    for (int k = 0; k < nk; ++k) {
+      const double x0 = a0[k], x1 = a1[k];
+#pragma unroll
+      for (int q = 0; q < MG_TJ; ++q) { const double y = b[q][k]; c0[q] += x0 * y; c1[q] += x1 * y; }
+    }
+#pragma unroll
+    for (int q = 0; q < MG_TJ; ++q) {
+      const int j = j0 + q * hj;
+      if (j < nj) { store(i0, j, c0[q]); if (ri) store(i1, j, c1[q]); }
+    }
   }
 }
 
 /* C(i, j) = base(i, j) + [sum_r G[r + ng * i] * (rho[r] * H[r + ng * j])] + sum_k A[i + lda * k] * B[k + ldb * j]
- * with the same 2 x 2 ownership; the bracket is skipped when G is null.  finish(i, j, gsum, sum)
+ * with the same 2 x 4 ownership; the bracket is skipped when G is null.  finish(i, j, gsum, sum)
  * combines and stores.  Summation orders per element are those of the plain loops. */
 template <class Finish>
 MG_DEV void tiled_nn_g(const double* A, int lda, int ni, const double* B, int ldb, int nj, int nk,
                        const double* G, const double* H, const double* rho, int ng, Finish finish) {
-  const int hi = (ni + 1) / 2, hj = (nj + 1) / 2;
+  const int hi = (ni + 1) / 2, hj = (nj + MG_TJ - 1) / MG_TJ;
   MG_PAR(te, hi * hj) {
-    const int i0 = te % hi, j0 = te / hi, i1 = i0 + hi, j1 = j0 + hj;
-    const bool ri = i1 < ni, rj = j1 < nj;
-    const int i1c = ri ? i1 : i0, j1c = rj ? j1 : j0;
-    double g00 = 0.0, g10 = 0.0, g01 = 0.0, g11 = 0.0;
+    const int i0 = te % hi, j0 = te / hi, i1 = i0 + hi;
+    const bool ri = i1 < ni;
+    const int i1c = ri ? i1 : i0;
+    int jc[MG_TJ];
+    double g0[MG_TJ], g1[MG_TJ], c0[MG_TJ], c1[MG_TJ];
+#pragma unroll
+    for (int q = 0; q < MG_TJ; ++q) {
+      const int j = j0 + q * hj;
+      jc[q] = j < nj ? j : j0;
+      g0[q] = 0.0; g1[q] = 0.0; c0[q] = 0.0; c1[q] = 0.0;
+    }
     if (G) {
       const double *p0 = G + (size_t)ng * i0, *p1 = G + (size_t)ng * i1c;
-      const double *q0 = H + (size_t)ng * j0, *q1 = H + (size_t)ng * j1c;
       for (int r = 0; r < ng; ++r) {
-        const double x0 = p0[r], x1 = p1[r], y0 = rho[r] * q0[r], y1 = rho[r] * q1[r];
-        g00 += x0 * y0; g10 += x1 * y0; g01 += x0 * y1; g11 += x1 * y1;
+        const double x0 = p0[r], x1 = p1[r], rr = rho[r];
+#pragma unroll
+        for (int q = 0; q < MG_TJ; ++q) { const double y = rr * H[r + (size_t)ng * jc[q]]; g0[q] += x0 * y; g1[q] += x1 * y; }
       }
     }
-    const double *b0 = B + (size_t)ldb * j0, *b1 = B + (size_t)ldb * j1c;
-    double c00 = 0.0, c10 = 0.0, c01 = 0.0, c11 = 0.0;
     for (int k = 0; k < nk; ++k) {
-      const double x0 = A[i0 + (size_t)lda * k], x1 = A[i1c + (size_t)lda * k], y0 = b0[k], y1 = b1[k];
-      c00 += x0 * y0; c10 += x1 * y0; c01 += x0 * y1; c11 += x1 * y1;
+      const double x0 = A[i0 + (size_t)lda * k], x1 = A[i1c + (size_t)lda * k];
+#pragma unroll
+      for (int q = 0; q < MG_TJ; ++q) { const double y = B[k + (size_t)ldb * jc[q]]; c0[q] += x0 * y; c1[q] += x1 * y; }
     }
-    finish(i0, j0, g00, c00);
-    if (ri) finish(i1, j0, g10, c10);
-    if (rj) finish(i0, j1, g01, c01);
-    if (ri && rj) finish(i1, j1, g11, c11);
+#pragma unroll
+    for (int q = 0; q < MG_TJ; ++q) {
+      const int j = j0 + q * hj;
+      if (j < nj) { finish(i0, j, g0[q], c0[q]); if (ri) finish(i1, j, g1[q], c1[q]); }
+    }
   }
 }
 
