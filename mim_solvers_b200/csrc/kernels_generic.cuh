@@ -219,7 +219,7 @@ MG_DEV void llt_solve_multi(const double* L, int n, double* b, int nrhs, int inc
  * instead of two feeding one, lanes still walk consecutive i (same bank pattern as one element per
  * thread) and the B operands are warp broadcasts.  Every element keeps its own k-ascending sum,
  * so results are bit-identical to the plain loop. */
-#define MG_TJ 4
+#define MG_TJ 8
 template <class Store>
 MG_DEV void tiled_tn(const double* A, int lda, int ni, const double* B, int ldb, int nj, int nk, Store store) {
   const int hi = (ni + 1) / 2, hj = (nj + MG_TJ - 1) / MG_TJ;

@@ -408,8 +408,8 @@ __device__ __forceinline__ void small_forward_gj(const Prob& p, const double* pk
     if (t + 1 < T) prefetch(t + 1, s ^ 1);
     mbar_wait(bars + s, (uint32_t)(j >> 1) & 1u);
     if (gx) { xg += fabs(x_cur); gap += fabs(fs_cur); kkt = nmax(kkt, fabs(fs_cur)); }
-    /* du = -K dx - k  (src/sqp.cpp:285-286) */
-    {
+    /* du = -K dx - k  (src/sqp.cpp:285-286); idle lanes are predicated off (no shared-memory wavefronts) */
+    if (gu) {
       double a0 = 0.0, a1 = 0.0;
 #pragma unroll
       for (int i = 0; i < NX; i += 2) {
@@ -419,13 +419,13 @@ __device__ __forceinline__ void small_forward_gj(const Prob& p, const double* pk
         a1 = fma(k2.y, x2.y, a1);
       }
       const double v = -(a0 + a1) - st[C::fk + lu];
-      if (gu) { sU[lane] = v; p.du[(size_t)t * NU + lane] = v; ug += fabs(v); }
+      sU[lane] = v; p.du[(size_t)t * NU + lane] = v; ug += fabs(v);
     }
     __syncwarp();
     /* dx+ = fs+ + Fu du + Fx dx  (src/sqp.cpp:287-289) */
-    const double fs_n = st[C::fFs + lx];
-    double x_n;
-    {
+    double fs_n = 0.0, x_n = 0.0;
+    if (gx) {
+      fs_n = st[C::fFs + lx];
       double a0 = 0.0, a1 = 0.0;
 #pragma unroll
       for (int a = 0; a < NU; a += 2) {
@@ -441,13 +441,13 @@ __device__ __forceinline__ void small_forward_gj(const Prob& p, const double* pk
         b1 = fma(st[C::fF + lx + NX * (jj + 1)], x2.y, b1);
       }
       x_n = (fs_n + (a0 + a1)) + (b0 + b1);
-      if (gx) { p.dx[(size_t)(t + 1) * NX + lane] = x_n; sXn[lane] = x_n - fs_n; }
+      p.dx[(size_t)(t + 1) * NX + lane] = x_n; sXn[lane] = x_n - fs_n;
     }
     __syncwarp();
     /* lag_mul+ = Vxx+ (dx+ - fs+) + Vx+  (src/sqp.cpp:282-284, 296-298); Vxx+ is symmetric
      * to rounding, so lane i reads its row as the contiguous column i */
-    double lam_n;
-    {
+    double lam_n = 0.0;
+    if (gx) {
       double a0 = 0.0, a1 = 0.0;
 #pragma unroll
       for (int jj = 0; jj < NX; jj += 2) {
@@ -457,11 +457,11 @@ __device__ __forceinline__ void small_forward_gj(const Prob& p, const double* pk
         a1 = fma(v2.y, y2.y, a1);
       }
       lam_n = (a0 + a1) + st[C::fVx + lx];
-      if (gx) { p.lag[(size_t)(t + 1) * NX + lane] = lam_n; sLam[lane] = lam_n; }
+      p.lag[(size_t)(t + 1) * NX + lane] = lam_n; sLam[lane] = lam_n;
     }
     __syncwarp();
     /* stationarity rows of knot t  (src/sqp.cpp:249-258) */
-    {
+    if (gc) {
       double a0 = 0.0, a1 = 0.0;
 #pragma unroll
       for (int k = 0; k < NX; k += 2) {
@@ -472,7 +472,7 @@ __device__ __forceinline__ void small_forward_gj(const Prob& p, const double* pk
       }
       double v = st[C::fL + lc] + (a0 + a1);
       if (gx) v -= lam;
-      if (gc) kkt = nmax(kkt, fabs(v));
+      kkt = nmax(kkt, fabs(v));
     }
     if (gx) sX[lane] = x_n;
     x_cur = x_n; fs_cur = fs_n; lam = lam_n;
