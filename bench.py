@@ -403,9 +403,6 @@ def main():
         import torch
         import torch.distributed as dist
         torch.cuda.set_device(local_rank)
-        # NCCL prints its version banner on STDOUT at NCCL_DEBUG=VERSION: keep stdout to the one JSON line
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     try:
         gpu_arm(args, rank, world, local_rank)
@@ -415,5 +412,16 @@ def main():
             dist.destroy_process_group()
 
 
+def _json_only_stdout():
+    """Libraries (NCCL's version banner) write to file descriptor 1 directly: point fd 1 at stderr for
+    the whole run and give Python's sys.stdout a private copy of the real stdout, so that the one JSON
+    line is the only thing the driver reads there."""
+    sys.stdout.flush()
+    real = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real, "w", buffering=1)
+
+
 if __name__ == "__main__":
+    _json_only_stdout()
     main()

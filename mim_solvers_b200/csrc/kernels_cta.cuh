@@ -50,8 +50,8 @@ template <> struct StreamTune<36, 12> { static constexpr int MAXT = 192, MINB = 
 template <> struct StreamTune<12, 6> { static constexpr int MAXT = 96, MINB = MIMGPU_TUNE_C1_MINB; };
 template <> struct StreamTune<32, 16> { static constexpr int MAXT = 192, MINB = 2; };
 /* DIRECT shapes: one CTA per SM (the Riccati layout of the full sweeps fills the shared memory) */
-template <> struct StreamTune<64, 32> { static constexpr int MAXT = 256, MINB = 1; };
-template <> struct StreamTune<76, 32> { static constexpr int MAXT = 256, MINB = 1; };
+template <> struct StreamTune<64, 32> { static constexpr int MAXT = 384, MINB = 1; };
+template <> struct StreamTune<76, 32> { static constexpr int MAXT = 384, MINB = 1; };
 template <> struct StreamTune<48, 24> { static constexpr int MAXT = 256, MINB = 1; };
 
 template <int NX, int NU, int SPLIT, bool DIRECT = false>

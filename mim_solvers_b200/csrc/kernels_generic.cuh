@@ -291,6 +291,27 @@ MG_DEV void tiled_nn_g(const double* A, int lda, int ni, const double* B, int ld
 /* One right-hand side, column-oriented so that the CTA shares the work; every x[i]
  * still subtracts its terms in the reference's order (j ascending / descending). */
 MG_DEV void llt_solve_one(const double* L, int n, double* x) {
+#ifndef MIMGPU_EMU
+  if (n <= 32) { /* one warp, x in registers: same operations per element, no CTA barrier per column */
+    if (threadIdx.x < 32) {
+      const int i = threadIdx.x;
+      double xi = (i < n) ? x[i] : 0.0;
+      for (int j = 0; j < n; ++j) {
+        const double xj = __shfl_sync(0xffffffffu, xi, j) / L[j + n * j];
+        if (i == j) xi = xj;
+        if (i > j && i < n) xi -= L[i + n * j] * xj;
+      }
+      for (int j = n - 1; j >= 0; --j) {
+        const double xj = __shfl_sync(0xffffffffu, xi, j) / L[j + n * j];
+        if (i == j) xi = xj;
+        if (i < j) xi -= L[j + n * i] * xj;
+      }
+      if (i < n) x[i] = xi;
+    }
+    MG_SYNC();
+    return;
+  }
+#endif
   for (int j = 0; j < n; ++j) {
     MG_SINGLE { x[j] = x[j] / L[j + n * j]; }
     MG_SYNC();
