@@ -40,6 +40,9 @@ struct StreamKPar {
 template <int NX, int NU> struct StreamTune {
   static constexpr int MAXT = NX <= 16 ? 128 : 256, MINB = NX <= 16 ? 6 : 2;
 };
+#ifndef MIMGPU_STREAM_MAX_STAGES
+#define MIMGPU_STREAM_MAX_STAGES 3   /* the pipeline has barriers for 4; 4 stages not measured yet */
+#endif
 #ifndef MIMGPU_TUNE_C3_MINB
 #define MIMGPU_TUNE_C3_MINB 2
 #endif
@@ -173,7 +176,7 @@ static StreamPlan stream_plan_t(const mimgpu_shape& sh, int stage_fx, int max_sm
   pl.nt = nt;
   const int nvmax = StreamCfg<NX, NU>::VPT * nt;
   if (StreamCfg<NX, NU>::nv_bwd(sh.ng) > nvmax || StreamCfg<NX, NU>::nv_fwd(ngm) > nvmax) return pl;
-  for (int ns = 3; ns >= 2; --ns) {
+  for (int ns = MIMGPU_STREAM_MAX_STAGES; ns >= 2; --ns) {
     const StreamSmem ss = stream_layout<NX, NU>(sh.ng, sh.ngT, ns, pl.generic_total);
     /* more than two stages only while the shape's target of resident CTAs still fits an SM */
     const int bytes = ss.total * 8;
