@@ -31,6 +31,17 @@ def build_emu(force=False) -> Path:
     return EMU_BIN
 
 
+def build_api_emu(force=False) -> Path:
+    out = _BUILD / "test_api_emu"
+    deps = [_HDRS[0], _HDRS[1], _DIR / "test_api.cpp", _DIR / "mimgpu_emu_shim.cpp",
+            _ROOT / "mim_solvers_b200" / "csrc" / "kernels_generic.cuh"]
+    if force or _stale(out, deps):
+        _BUILD.mkdir(exist_ok=True)
+        subprocess.run(["g++", "-O1", "-g", "-std=c++17", "-ffp-contract=off", "-o", str(out),
+                        str(_DIR / "test_api.cpp"), str(_DIR / "mimgpu_emu_shim.cpp")], check=True)
+    return out
+
+
 def build_gpu(force=False) -> Path:
     """g++ only: the driver links the prebuilt libmimgpu.so (rpath relative to the binary)."""
     lib = _ROOT / "mim_solvers_b200" / "csrc" / "libmimgpu.so"

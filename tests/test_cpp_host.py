@@ -42,3 +42,12 @@ def test_cpp_host_has_no_cpu_fallback(tmp_path):
     cpp_host.write_problem(tmp_path / "p.bin", sc.make_lq(B=1, T=3))
     r = subprocess.run([str(b), "sqp", str(tmp_path / "p.bin"), str(tmp_path / "o.bin")], capture_output=True, text=True)
     assert r.returncode == 3 and "mimgpu_create failed" in r.stderr, (r.returncode, r.stderr)
+
+
+def test_cpp_api_defaults_and_argument_checks():
+    """tests/cpp/test_api.cpp: reference defaults (tests/test_solvers.cpp:83-112), invalid arguments
+    throw std::invalid_argument (src/ddp.cpp:547-638, src/sqp.cpp:308-311), tiny solves."""
+    import subprocess
+    b = cpp_host.build_api_emu()
+    r = subprocess.run([str(b)], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and r.stdout.strip().endswith("OK"), (r.stdout, r.stderr)
