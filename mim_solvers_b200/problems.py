@@ -246,6 +246,9 @@ CONFIGS = {
     "C1_ur5_csqp": dict(T=40, nx=12, nu=6, ng=3, ngT=3, box_rows=0),
     "C2_ur5_sqp": dict(T=100, nx=12, nu=6),
     "C3_solo12_csqp": dict(T=100, nx=36, nu=12, ng=16, ngT=0, box_rows=12),
+    # C3 without currently-violated rows: the ADMM loop converges at the default tolerances with
+    # data-dependent iteration counts (200..650) -- the threshold-driven parity / bench case
+    "C3_solo12_tol": dict(T=100, nx=36, nu=12, ng=16, ngT=0, box_rows=12, violate_frac=0.0),
     "C3b_solo12_bench": dict(T=50, nx=36, nu=12, ng=36, ngT=36, box_rows=36),
     "C5_talos_csqp": dict(T=100, nx=76, nu=32, ng=32, ngT=0, box_rows=32),
     "C5_talos_sqp": dict(T=120, nx=76, nu=32),

@@ -39,3 +39,18 @@ def test_emu_vs_oracle_random(emu, oracle_lib, stage_fx):
     compare_engines_sqp(mk_e, mk_o, make_random_batch(3, 9, 6, 3))
     compare_engines_fddp(mk_e, mk_o, make_random_batch(2, 7, 5, 2))
     compare_engines_csqp(mk_e, mk_o, make_random_batch(3, 8, 6, 3, ng=5, ngT=4, eq_frac=0.1))
+
+
+def test_emu_vs_oracle_rho_heuristic(emu, oracle_lib):
+    """update_rho_with_heuristic branch of update_lagrangian_parameters (src/csqp.cpp:1245-1257):
+    dual norms without the G^T products; kernel source (host emulation) against the oracle."""
+    from mim_solvers_b200 import _capi
+    from mim_solvers_b200.problems import make_random_batch
+    p = _capi.default_csqp_params(update_rho_with_heuristic=1, max_qp_iters=300)
+    batch = make_random_batch(4, 10, 6, 3, ng=4, ngT=3, violate_frac=0.0)
+    a, b = compare_engines_csqp(lambda x: emu.EmuEngine(x), lambda x: oracle_lib.Oracle(x, nthreads=1), batch, params=p)
+    p0 = _capi.default_csqp_params(max_qp_iters=300)
+    c = oracle_lib.Oracle(batch, nthreads=1)
+    c.csqp_calc_norms(); c.csqp_reset_rho(p0); c.csqp_direction(p0)
+    # the branch is really taken: the heuristic norms differ from the G^T-product norms
+    assert not np.allclose(b.scalar("norm_dual"), c.scalar("norm_dual"))

@@ -60,13 +60,15 @@ def test_fullsize_sqp(eng, oracle_lib, name, B, nsub):
     o = oracle_lib.Oracle(sub)
     o.sqp_direction()
     for f in ("dx", "du", "lag_mul", "Vxx", "Vx", "K", "k"):
-        assert_close(g.field(f)[:nsub], o.field(f), TOL, f"{name} {f}")
+        assert_close(g.field(f)[:nsub], o.field(f), TOL, f"{name} {f}", per_problem=True)
     for s in ("KKT", "gap_norm", "merit", "x_grad_norm", "u_grad_norm"):
-        assert_close(g.scalar(s)[:nsub], o.scalar(s), TOL, f"{name} {s}")
+        assert_close(g.scalar(s)[:nsub], o.scalar(s), TOL, f"{name} {s}", per_problem=True)
     _sqp_properties(batch, g)
 
 
-@pytest.mark.parametrize("name,B,nsub", [("C1_ur5_csqp", 512, 16), ("C3_solo12_csqp", 64, 4), ("C3b_solo12_bench", 64, 4)])
+@pytest.mark.parametrize("name,B,nsub", [("C1_ur5_csqp", 512, 16), ("C3_solo12_csqp", 64, 4), ("C3b_solo12_bench", 64, 4),
+                                         ("C5_talos_csqp", 32, 2), ("C4_clq_nx32", 64, 4), ("C4_clq_nx64", 32, 2),
+                                         ("C4_clq_nx16", 128, 8)])
 def test_fullsize_csqp_protocol(eng, oracle_lib, name, B, nsub):
     """The benchmark protocol (benchmarks/solo12.cpp:213-216: 50 ADMM iterations, eps = 0, no
     equality-QP guess) on the bench's own generator; every problem runs the 50 iterations, the
@@ -84,9 +86,9 @@ def test_fullsize_csqp_protocol(eng, oracle_lib, name, B, nsub):
     o.csqp_direction(p, with_kkt=True)
     assert np.array_equal(np.asarray(o.qp_iters), g.qp_iters[:nsub])
     for f in ("dx_tilde", "du_tilde", "lag_mul", "y", "z", "rho_vec"):
-        assert_close(g.field(f)[:nsub], o.field(f), TOL, f"{name} {f}")
+        assert_close(g.field(f)[:nsub], o.field(f), TOL, f"{name} {f}", per_problem=True)
     for s in ("KKT", "rho_sparse", "norm_primal", "norm_dual"):
-        assert_close(g.scalar(s)[:nsub], o.scalar(s), TOL, f"{name} {s}")
+        assert_close(g.scalar(s)[:nsub], o.scalar(s), TOL, f"{name} {s}", per_problem=True)
     dxt, dut = g.field("dx_tilde"), g.field("du_tilde")
     nxt = np.einsum("btij,btj->bti", batch.mat("Fx"), dxt[:, :-1]) + np.einsum("btij,btj->bti", batch.mat("Fu"), dut) \
         + batch.arrays["fs"][:, 1:]
@@ -95,6 +97,41 @@ def test_fullsize_csqp_protocol(eng, oracle_lib, name, B, nsub):
     z = g.field("z")[:, :T * ng].reshape(B, T, ng)
     lo, hi = batch.arrays["g_lb"] - batch.arrays["g"], batch.arrays["g_ub"] - batch.arrays["g"]
     assert np.all(z >= lo - 1e-12 * np.maximum(1.0, np.abs(lo))) and np.all(z <= hi + 1e-12 * np.maximum(1.0, np.abs(hi)))
+
+
+@pytest.mark.parametrize("name,B,nsub,heur", [("C3_solo12_tol", 64, 16, 0), ("C1_ur5_csqp", 256, 64, 0),
+                                              ("C3_solo12_csqp", 32, 4, 0), ("C1_ur5_csqp", 64, 32, 1),
+                                              ("C3_solo12_tol", 32, 8, 1)])
+def test_fullsize_csqp_default_tolerances(eng, oracle_lib, name, B, nsub, heur):
+    """Threshold-driven ADMM (src/csqp.cpp:497-511, 519-532): default eps_abs = eps_rel = 1e-4,
+    max_qp_iters = 1000, equality-QP guess, adaptive rho; heur = 1 also exercises
+    update_rho_with_heuristic (src/csqp.cpp:1245-1257).  qp_iters / converged are compared
+    problem by problem and every mismatch is listed."""
+    batch = make_config(name, B)
+    p = _capi.default_csqp_params(update_rho_with_heuristic=heur)
+    g = eng(batch)
+    g.csqp_calc_norms(); g.csqp_reset_rho(p)
+    g.csqp_direction(p, with_kkt=True)
+    assert not g.status.any()
+    sub = batch.subset(np.arange(nsub))
+    o = oracle_lib.Oracle(sub)
+    o.csqp_calc_norms(); o.csqp_reset_rho(p)
+    o.csqp_direction(p, with_kkt=True)
+    gi, oi = g.qp_iters[:nsub], np.asarray(o.qp_iters)
+    bad = [(int(b), int(gi[b]), int(oi[b])) for b in np.nonzero(gi != oi)[0]]
+    assert not bad, f"{name}: qp_iters mismatches (problem, gpu, oracle): {bad}"
+    assert np.array_equal(g.converged[:nsub], np.asarray(o.converged))
+    if name != "C3_solo12_csqp":   # (its violated rows keep every problem at max_qp_iters + 1)
+        assert len(set(oi.tolist())) > 1, "iteration counts should be data-dependent"
+    for f in ("dx_tilde", "du_tilde", "lag_mul", "y", "z", "rho_vec"):
+        assert_close(g.field(f)[:nsub], o.field(f), TOL, f"{name} {f}", per_problem=True)
+    for s in ("KKT", "rho_sparse", "norm_primal", "norm_dual", "norm_primal_rel", "norm_dual_rel"):
+        assert_close(g.scalar(s)[:nsub], o.scalar(s), TOL, f"{name} {s}", per_problem=True)
+    # second call on the same objects: warm-started y / rho (solver members persist, csqp.hpp:250-357)
+    g.csqp_direction(p, with_kkt=True); o.csqp_direction(p, with_kkt=True)
+    assert np.array_equal(g.qp_iters[:nsub], np.asarray(o.qp_iters))
+    for f in ("dx_tilde", "du_tilde", "y", "z"):
+        assert_close(g.field(f)[:nsub], o.field(f), TOL, f"{name} warm {f}", per_problem=True)
 
 
 def test_fullsize_tiled_batches_are_identical(eng):

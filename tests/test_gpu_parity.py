@@ -68,6 +68,17 @@ def test_gpu_csqp_vs_oracle(eng, oracle_lib, B, T, nx, nu, ng, ngT, kw):
     compare_engines_csqp(lambda b: eng(b), lambda b: oracle_lib.Oracle(b), batch, params=p, n_calls=2)
 
 
+@pytest.mark.parametrize("B,T,nx,nu,ng,ngT,kw", [(6, 40, 12, 6, 3, 3, dict(box_rows=0)), (3, 12, 36, 12, 16, 0, dict(box_rows=12)),
+                                                 (2, 6, 64, 32, 40, 16, {}), (3, 9, 7, 3, 5, 2, {})])
+def test_gpu_csqp_rho_heuristic(eng, oracle_lib, B, T, nx, nu, ng, ngT, kw):
+    """update_rho_with_heuristic = 1 (src/csqp.cpp:1245-1257) on the streaming, direct and generic kernels."""
+    from mim_solvers_b200 import _capi
+    from mim_solvers_b200.problems import make_random_batch
+    batch = make_random_batch(B, T, nx, nu, ng=ng, ngT=ngT, violate_frac=0.0, **kw)
+    p = _capi.default_csqp_params(max_qp_iters=300, update_rho_with_heuristic=1)
+    compare_engines_csqp(lambda b: eng(b), lambda b: oracle_lib.Oracle(b), batch, params=p, n_calls=2)
+
+
 @pytest.mark.parametrize("B,T,nx,nu,ng,ngT", [(16, 12, 76, 32, 32, 0), (8, 9, 48, 24, 30, 20), (16, 12, 36, 12, 16, 0)])
 def test_gpu_csqp_device_attached_separate_allocations(oracle_lib, B, T, nx, nu, ng, ngT):
     """Each derivative array in its own cudaMalloc block (the caller-owned layout of the drop-in): an index one
