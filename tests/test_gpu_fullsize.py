@@ -31,6 +31,17 @@ def _rel(a, b):
     return np.abs(a - b).max() / max(1.0, np.abs(b).max())
 
 
+def _assert_norms(g, o, nsub, name):
+    """ADMM residual norms: |c - z| and |G^T rho dz| are differences of O(1) quantities (they reach
+    1e-11 on converged problems), so they are compared at 1e-9 of max(1, |value|) per problem --
+    the scale of c, z, y they are formed from -- not relative to themselves."""
+    for s in ("norm_primal", "norm_dual", "norm_primal_rel", "norm_dual_rel"):
+        x, y = g.scalar(s)[:nsub], o.scalar(s)
+        assert np.array_equal(np.isfinite(x), np.isfinite(y)), f"{name} {s}"
+        fin = np.isfinite(y)
+        assert np.all(np.abs(x[fin] - y[fin]) <= TOL * np.maximum(1.0, np.abs(y[fin]))), (name, s, x, y)
+
+
 def _sqp_properties(batch, g):
     dx, du, lam = g.field("dx"), g.field("du"), g.field("lag_mul")
     Fx, Fu, fs = batch.mat("Fx"), batch.mat("Fu"), batch.arrays["fs"]
@@ -87,8 +98,9 @@ def test_fullsize_csqp_protocol(eng, oracle_lib, name, B, nsub):
     assert np.array_equal(np.asarray(o.qp_iters), g.qp_iters[:nsub])
     for f in ("dx_tilde", "du_tilde", "lag_mul", "y", "z", "rho_vec"):
         assert_close(g.field(f)[:nsub], o.field(f), TOL, f"{name} {f}", per_problem=True)
-    for s in ("KKT", "rho_sparse", "norm_primal", "norm_dual"):
+    for s in ("KKT", "rho_sparse"):
         assert_close(g.scalar(s)[:nsub], o.scalar(s), TOL, f"{name} {s}", per_problem=True)
+    _assert_norms(g, o, nsub, name)
     dxt, dut = g.field("dx_tilde"), g.field("du_tilde")
     nxt = np.einsum("btij,btj->bti", batch.mat("Fx"), dxt[:, :-1]) + np.einsum("btij,btj->bti", batch.mat("Fu"), dut) \
         + batch.arrays["fs"][:, 1:]
@@ -125,8 +137,9 @@ def test_fullsize_csqp_default_tolerances(eng, oracle_lib, name, B, nsub, heur):
         assert len(set(oi.tolist())) > 1, "iteration counts should be data-dependent"
     for f in ("dx_tilde", "du_tilde", "lag_mul", "y", "z", "rho_vec"):
         assert_close(g.field(f)[:nsub], o.field(f), TOL, f"{name} {f}", per_problem=True)
-    for s in ("KKT", "rho_sparse", "norm_primal", "norm_dual", "norm_primal_rel", "norm_dual_rel"):
+    for s in ("KKT", "rho_sparse"):
         assert_close(g.scalar(s)[:nsub], o.scalar(s), TOL, f"{name} {s}", per_problem=True)
+    _assert_norms(g, o, nsub, name)
     # second call on the same objects: warm-started y / rho (solver members persist, csqp.hpp:250-357)
     g.csqp_direction(p, with_kkt=True); o.csqp_direction(p, with_kkt=True)
     assert np.array_equal(g.qp_iters[:nsub], np.asarray(o.qp_iters))
