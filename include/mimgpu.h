@@ -38,7 +38,7 @@
 extern "C" {
 #endif
 
-#define MIMGPU_ABI_VERSION 1
+#define MIMGPU_ABI_VERSION 2
 
 /* ---- return codes ------------------------------------------------------ */
 #define MIMGPU_OK 0
@@ -96,7 +96,28 @@ typedef struct {
 
 #define MIMGPU_MEM_HOST 0   /* pointers are host memory: async H2D copy      */
 #define MIMGPU_MEM_DEVICE 1 /* pointers are device memory in the layout above:
-                               attached zero-copy, caller keeps them alive    */
+                               attached zero-copy, caller keeps them alive and
+                               may update them IN PLACE between direction
+                               calls: every direction call re-reads them (for
+                               the small shapes this includes the re-layout
+                               into knot records -- use mimgpu_upload_records
+                               to skip that pass)                             */
+
+/* Knot-record input layout (the HBM layout the warp-per-problem SQP kernel reads; available for
+ * the shapes mimgpu_get_record_layout accepts, ng = ngT = 0).  One problem = T running-knot records
+ * followed by one terminal record, problems back to back:
+ *   running knot t : [fs_t | Lxx Lxu | Luu | Lx Lu | Fx Fu]   every block dense column-major
+ *   terminal       : [fs_T | Lxx_T | Lx_T]
+ * A packer writes each ActionData block with one memcpy at base + b * problem_doubles +
+ * t * rec_doubles + off_*, exactly as it would into the field-major arrays. */
+typedef struct {
+  int32_t rec_doubles;     /* doubles of one running-knot record                    */
+  int32_t term_doubles;    /* doubles of the terminal record                        */
+  int32_t problem_doubles; /* T * rec_doubles + term_doubles                        */
+  int32_t off_fs, off_Lxx, off_Lxu, off_Luu, off_Lx, off_Lu, off_Fx, off_Fu; /* in a running record */
+  int32_t toff_fs, toff_Lxx, toff_Lx;                                          /* in the terminal record */
+  int32_t reserved[2];
+} mimgpu_record_layout;
 
 /* SolverSQP / SolverFDDP direction parameters (src/sqp.cpp:91-97,224-242). */
 typedef struct {
@@ -194,6 +215,19 @@ int mimgpu_get_shape(const mimgpu_ctx* ctx, mimgpu_shape* shape);
 int mimgpu_upload(mimgpu_ctx* ctx, const mimgpu_derivs* derivs, int memkind,
                   void* cuda_stream);
 
+/* Block offsets of the knot-record layout for this ctx's shape; MIMGPU_ERR_UNSUPPORTED when the
+ * shape is not served by the record kernel (use mimgpu_upload then). */
+int mimgpu_get_record_layout(const mimgpu_ctx* ctx, mimgpu_record_layout* out);
+
+/* Same upload point as mimgpu_upload (right after problem_->calcDiff, src/ddp.cpp:253-263) for a
+ * producer that writes knot records: `records` = [B][problem_doubles], `cost` = [B] or NULL.
+ * MIMGPU_MEM_DEVICE: attached zero-copy (16-byte aligned), the kernel reads the caller's memory at
+ * every direction call and there is NO re-layout pass.  MIMGPU_MEM_HOST: one async H2D copy.
+ * Entry points the record kernel does not serve (FDDP, CSQP with ng = 0, downloads of Qu_ / Quuk_ /
+ * Quu_llt_) rebuild the field-major arrays on the device first. */
+int mimgpu_upload_records(mimgpu_ctx* ctx, const double* records, const double* cost, int memkind,
+                          void* cuda_stream);
+
 /* Per-problem regularisation (solver members preg_/dreg_, src/ddp.cpp:431-445)
  * for batches whose problems are at different regularisation levels.  NULL
  * restores the scalar values of the params struct.  Host pointers, [B]. */
@@ -229,6 +263,12 @@ int mimgpu_sqp_direction_host(mimgpu_ctx* ctx, const mimgpu_derivs* host_derivs,
                               const mimgpu_sqp_params* p, double* dx, double* du,
                               double* lag_mul, double* kkt, int32_t n_chunks);
 
+/* The same for host-resident KNOT RECORDS ([B][problem_doubles], cost [B] or NULL): no re-layout
+ * kernel at all, one H2D copy per slice. */
+int mimgpu_sqp_direction_host_records(mimgpu_ctx* ctx, const double* records, const double* cost,
+                                      const mimgpu_sqp_params* p, double* dx, double* du,
+                                      double* lag_mul, double* kkt, int32_t n_chunks);
+
 /* SolverFDDP::computeDirection (src/fddp.cpp:189-204) without calcDiff +
  * updateExpectedImprovement (src/fddp.cpp:256-279): backward pass, gap_norm_,
  * dg_, dq_.  Vxx, Vx, K, k, Qu, Quuk stay on the device for download. */
@@ -261,9 +301,11 @@ int mimgpu_csqp_direction(mimgpu_ctx* ctx, const mimgpu_csqp_params* p,
 /* Copies one solver member of all B problems to host memory `dst`
  * (async on `stream`; synchronise the stream before reading). */
 int mimgpu_download(mimgpu_ctx* ctx, int field, double* dst, void* cuda_stream);
-/* Device pointer of a field (for callers that keep results on the GPU). */
+/* Device pointer of a field (for callers that keep results on the GPU).  Members the fast SQP
+ * kernel materialises lazily (Vxx_ Vx_ K_ k_ from its spill records; Qu_ Quuk_ Quu_llt_ by a
+ * recomputation) are produced by work enqueued on `cuda_stream`: order later reads after it. */
 int mimgpu_field_ptr(mimgpu_ctx* ctx, int field, double** dev_ptr,
-                     int64_t* n_doubles);
+                     int64_t* n_doubles, void* cuda_stream);
 /* Per-problem scalars: dst [B] doubles. */
 int mimgpu_scalar(mimgpu_ctx* ctx, int which, double* dst, void* cuda_stream);
 /* qp_iters[B] (CSQP; 0 for SQP) and status[B]; either may be NULL. */

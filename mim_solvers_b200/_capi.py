@@ -72,6 +72,13 @@ class CsqpParams(C.Structure):
         "reset_rho", "update_rho_with_heuristic", "warm_start_y", "reserved")]
 
 
+class RecordLayout(C.Structure):
+    """mimgpu_record_layout: block offsets (doubles) of the knot-record input layout."""
+    _fields_ = [(n, C.c_int32) for n in (
+        "rec_doubles", "term_doubles", "problem_doubles", "off_fs", "off_Lxx", "off_Lxu", "off_Luu",
+        "off_Lx", "off_Lu", "off_Fx", "off_Fu", "toff_fs", "toff_Lxx", "toff_Lx")] + [("reserved", C.c_int32 * 2)]
+
+
 class Summary(C.Structure):
     _fields_ = [("max_kkt", C.c_double), ("sum_qp_iters", C.c_int64),
                 ("max_qp_iters", C.c_int64), ("n_converged", C.c_int64),
@@ -106,7 +113,8 @@ SYMBOLS = (
     "mimgpu_abi_version", "mimgpu_device_count", "mimgpu_last_error", "mimgpu_create",
     "mimgpu_destroy", "mimgpu_get_shape", "mimgpu_upload", "mimgpu_set_reg",
     "mimgpu_set_active", "mimgpu_set_field", "mimgpu_sqp_direction",
-    "mimgpu_sqp_direction_host", "mimgpu_fddp_direction", "mimgpu_csqp_calc_norms", "mimgpu_csqp_reset_rho",
+    "mimgpu_sqp_direction_host", "mimgpu_sqp_direction_host_records", "mimgpu_get_record_layout",
+    "mimgpu_upload_records", "mimgpu_fddp_direction", "mimgpu_csqp_calc_norms", "mimgpu_csqp_reset_rho",
     "mimgpu_csqp_direction", "mimgpu_download", "mimgpu_field_ptr", "mimgpu_scalar",
     "mimgpu_iters_status", "mimgpu_converged", "mimgpu_summary_reduce", "mimgpu_launch_count", "mimgpu_stream_sync", "mimgpu_measure_peaks",
 )
@@ -129,12 +137,15 @@ def _declare(lib):
     lib.mimgpu_set_field.argtypes = [vp, C.c_int, vp, vp]
     lib.mimgpu_sqp_direction.argtypes = [vp, C.POINTER(SqpParams), vp]
     lib.mimgpu_sqp_direction_host.argtypes = [vp, C.POINTER(Derivs), C.POINTER(SqpParams), vp, vp, vp, vp, i32]
+    lib.mimgpu_sqp_direction_host_records.argtypes = [vp, vp, vp, C.POINTER(SqpParams), vp, vp, vp, vp, i32]
+    lib.mimgpu_get_record_layout.argtypes = [vp, C.POINTER(RecordLayout)]
+    lib.mimgpu_upload_records.argtypes = [vp, vp, vp, C.c_int, vp]
     lib.mimgpu_fddp_direction.argtypes = [vp, C.POINTER(SqpParams), vp]
     lib.mimgpu_csqp_calc_norms.argtypes = [vp, vp]
     lib.mimgpu_csqp_reset_rho.argtypes = [vp, C.POINTER(CsqpParams), vp]
     lib.mimgpu_csqp_direction.argtypes = [vp, C.POINTER(CsqpParams), C.c_int, vp]
     lib.mimgpu_download.argtypes = [vp, C.c_int, vp, vp]
-    lib.mimgpu_field_ptr.argtypes = [vp, C.c_int, C.POINTER(vp), C.POINTER(i64)]
+    lib.mimgpu_field_ptr.argtypes = [vp, C.c_int, C.POINTER(vp), C.POINTER(i64), vp]
     lib.mimgpu_scalar.argtypes = [vp, C.c_int, vp, vp]
     lib.mimgpu_iters_status.argtypes = [vp, vp, vp, vp]
     lib.mimgpu_converged.argtypes = [vp, vp, vp]

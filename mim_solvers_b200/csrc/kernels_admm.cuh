@@ -1,0 +1,764 @@
+/*
+ * kernels_admm.cuh -- the ADMM loop of SolverCSQP::computeDirection (src/csqp.cpp:454-517) with
+ * the light iterations CONDENSED on the closed-loop dynamics.
+ *
+ * Between two rho updates (rho_update_interval - 1 = 24 of every 25 iterations) the reference
+ * runs backwardPass_without_rho_update (src/csqp.cpp:1025-1108), forwardPass (:630-647) and
+ * update_lagrangian_parameters (:1196-1340) with K_t, LLT(Quu_t), Vxx_t frozen.  Written out,
+ * those two sweeps are LINEAR recurrences driven by the closed-loop matrix
+ *
+ *     Acl_t = Fx_t - Fu_t K_t                                   (frozen with K_t)
+ *
+ *   backward  Vx_t  = Qx_t - K_t^T Qu_t                         (src/csqp.cpp:1101-1104)
+ *                   = r_t + Acl_t^T tmp_t ,   tmp_t = Vx_{t+1} + Vxx_fs_t          (:1060)
+ *             r_t   = qx_t - K_t^T qu_t
+ *             qx_t  = Lx_t - sigma dx_t + Gx_t^T d_t   (t > 0),  d_t = y_t - rho_t o z_t  (:1068-1078)
+ *             qu_t  = Lu_t - sigma du_t + Gu_t^T d_t                               (:1083-1092)
+ *   gains     Qu_t  = qu_t + Fu_t^T tmp_t ,   k_t = Quu_t^-1 Qu_t                  (:1093-1097)
+ *   forward   dx~_{t+1} = b_t + Acl_t dx~_t ,  b_t = fs_{t+1} - Fu_t k_t           (:636-644)
+ *             du~_t = -k_t - K_t dx~_t
+ *
+ * so the only work that is SEQUENTIAL in t is one NX x NX mat-vec per knot and sweep (the two
+ * "chains"); everything else (r_t, qu_t, Qu_t, k_t, b_t, du~_t, the constraint rows c_t =
+ * Gx dx~ + Gu du~, the z / y projection and the residual norms) is independent across knots and
+ * runs warp-per-knot, streaming each of K, Gx, Gu, Fu, LLT once per iteration straight from
+ * global memory (coalesced, no shared-memory staging, many knots in flight per SM).  Per
+ * iteration and knot the kernel reads 2 NX^2 + 2 NX NU + NU^2 + ng (NX + NU) doubles instead of
+ * the 2 (NX^2 + 2 NX NU + ng (NX + NU)) + NU^2 of the sweep-by-sweep form, and the latency
+ * chain per knot drops from five dependent CTA-wide phases to one.  The arithmetic is the
+ * reference's up to the order of the floating-point sums (scripts/proto_condensed_admm.py:
+ * 1e-14 relative after 25 iterations on every BASELINE shape; parity bar 1e-9).
+ *
+ * Full sweeps (iteration k = 1 mod interval, src/csqp.cpp:477) keep the Riccati code of
+ * kernels_ric.cuh (DMMA) / kernels_generic.cuh; right after one, Acl_t (both orientations) and
+ * b_t are rebuilt from the fresh K_t, k_t.
+ */
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <type_traits>
+
+#include "launchers.h"
+#include "kernels_ric.cuh"
+
+namespace mimgpu {
+
+#define MG_FULLMASK 0xffffffffu
+
+/* ------------------------------------------------------------------ shared memory */
+struct AdmmSmem {
+  int bars, red, uni, vb, ws0, wsn, total;
+};
+template <int NX, int NU>
+__host__ __device__ inline AdmmSmem admm_layout(int ng, int ngT, int nwarps, int ric_total) {
+  AdmmSmem s;
+  const int ngm = ng > ngT ? ng : ngT;
+  s.bars = 0;
+  s.red = 8;
+  s.uni = 8 + 64;
+  s.vb = s.uni;                       /* chain vector, double buffered */
+  s.ws0 = s.uni + 2 * NX;             /* per-warp scratch of the knot-parallel phases */
+  s.wsn = (2 * NX + 2 * NU + 3 * ngm + 1) & ~1;
+  const int a = 2 * NX + nwarps * s.wsn;
+  s.total = s.uni + (a > ric_total ? a : ric_total);
+  return s;
+}
+/* per-warp scratch offsets */
+template <int NX, int NU>
+struct AdmmWs {
+  static constexpr int xs = 0, us = NX, qx = NX + NU, qu = 2 * NX + NU, ds = 2 * NX + 2 * NU;
+};
+
+/* --------------------------------------------------------------- warp primitives */
+/* y[o] = sum_k M[o * NIN + k] v[k], o < nrows: rows of M contiguous (16-byte aligned, NIN even),
+ * four lanes per row, eight rows per pass, 16-byte loads.  f(o, sum) runs on one lane per row. */
+template <int NIN, class F>
+__device__ __forceinline__ void wdot4(const double* M, int nrows, const double* v, int lane, F f) {
+  static_assert(NIN % 2 == 0, "16-byte row loads");
+  constexpr int KP = (NIN + 7) / 8;
+  const int g = lane >> 2, q = lane & 3;
+  for (int o0 = 0; o0 < nrows; o0 += 8) {
+    const int o = o0 + g;
+    const bool valid = o < nrows;
+    const double* row = M + (size_t)(valid ? o : 0) * NIN;
+    double a0 = 0.0, a1 = 0.0;
+#pragma unroll
+    for (int m = 0; m < KP; ++m) {
+      const int k = 2 * q + 8 * m;
+      if (k < NIN) {
+        const double2 mv = *reinterpret_cast<const double2*>(row + k);
+        const double2 vv = *reinterpret_cast<const double2*>(v + k);
+        a0 = fma(mv.x, vv.x, a0);
+        a1 = fma(mv.y, vv.y, a1);
+      }
+    }
+    double s = a0 + a1;
+    s += __shfl_xor_sync(MG_FULLMASK, s, 1);
+    s += __shfl_xor_sync(MG_FULLMASK, s, 2);
+    if (valid && q == 0) f(o, s);
+  }
+}
+
+/* Columns of a run-time-tall matrix against up to three vectors at once:
+ * s_e[o] = sum_r M[r + nin * o] v_e[r], o < nrows (column o of a col-major nin x nrows block).
+ * Vectors that are null are skipped.  f(o, s0, s1, s2) runs on one lane per column. */
+template <class F>
+__device__ __forceinline__ void wdot4_rt3(const double* M, int nrows, int nin, const double* v0, const double* v1,
+                                          const double* v2, int lane, F f) {
+  const int g = lane >> 2, q = lane & 3;
+  for (int o0 = 0; o0 < nrows; o0 += 8) {
+    const int o = o0 + g;
+    const bool valid = o < nrows;
+    const double* col = M + (size_t)(valid ? o : 0) * nin;
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0;
+    for (int r = q; r < nin; r += 4) {
+      const double mv = col[r];
+      if (v0) s0 = fma(mv, v0[r], s0);
+      if (v1) s1 = fma(mv, v1[r], s1);
+      if (v2) s2 = fma(mv, v2[r], s2);
+    }
+#pragma unroll
+    for (int off = 1; off <= 2; off <<= 1) {
+      s0 += __shfl_xor_sync(MG_FULLMASK, s0, off);
+      s1 += __shfl_xor_sync(MG_FULLMASK, s1, off);
+      s2 += __shfl_xor_sync(MG_FULLMASK, s2, off);
+    }
+    if (valid && q == 0) f(o, s0, s1, s2);
+  }
+}
+
+/* y[i] = sum_j M[i + NI * j] w[j], i < NI, j < NJ (col-major NI x NJ, lanes walk consecutive i:
+ * coalesced).  Shapes with NI <= 16 split the columns over 32 / NP lane groups.  f(i, sum) runs on
+ * one lane per row. */
+template <int NI, int NJ, class F>
+__device__ __forceinline__ void waxpy(const double* M, const double* w, int lane, F f) {
+  if constexpr (NI <= 16) {
+    constexpr int NP = NI <= 4 ? 4 : NI <= 8 ? 8 : 16, PH = 32 / NP;
+    const int i = lane % NP, ph = lane / NP;
+    const bool valid = i < NI;
+    const int ic = valid ? i : 0;
+    double a0 = 0.0;
+#pragma unroll
+    for (int j0 = 0; j0 < NJ; j0 += PH) {
+      const int j = j0 + ph;
+      if (j < NJ) a0 = fma(M[ic + NI * j], w[j], a0);
+    }
+#pragma unroll
+    for (int off = NP; off < 32; off <<= 1) a0 += __shfl_xor_sync(MG_FULLMASK, a0, off);
+    if (valid && ph == 0) f(i, a0);
+  } else {
+#pragma unroll
+    for (int i0 = 0; i0 < NI; i0 += 32) {
+      const int i = i0 + lane;
+      const bool valid = i < NI;
+      const int ic = valid ? i : 0;
+      double a0 = 0.0, a1 = 0.0;
+#pragma unroll 8
+      for (int j = 0; j + 1 < NJ; j += 2) {
+        a0 = fma(M[ic + NI * j], w[j], a0);
+        a1 = fma(M[ic + NI * (j + 1)], w[j + 1], a1);
+      }
+      if (NJ & 1) a0 = fma(M[ic + NI * (NJ - 1)], w[NJ - 1], a0);
+      if (valid) f(i, a0 + a1);
+    }
+  }
+}
+
+/* x := (L L^T)^-1 x for one right-hand side held one element per lane (NU <= 32), L = lower
+ * Cholesky factor, col-major NU x NU in global memory.  Column-oriented substitution: every
+ * x[i] subtracts its terms in the reference's order (Eigen LLT::solveInPlace, src/csqp.cpp:1096). */
+template <int NU>
+__device__ __forceinline__ double wsolve_llt(const double* L, double xi, int lane) {
+  static_assert(NU <= 32, "one lane per control");
+  const bool in = lane < NU;
+  const int lc = in ? lane : 0;
+  double lv[NU];
+#pragma unroll
+  for (int j = 0; j < NU; ++j) lv[j] = (in && lane >= j) ? L[lc + NU * j] : 1.0;   /* column entries of my row */
+#pragma unroll
+  for (int j = 0; j < NU; ++j) {
+    const double xj = __shfl_sync(MG_FULLMASK, xi / lv[j], j);
+    if (lane == j) xi = xj;
+    else if (lane > j) xi = fma(-lv[j], xj, xi);
+  }
+#pragma unroll
+  for (int j = 0; j < NU; ++j) lv[j] = (in && lane <= j) ? L[j + NU * lc] : 1.0;   /* row j, my column */
+#pragma unroll
+  for (int j = NU - 1; j >= 0; --j) {
+    const double xj = __shfl_sync(MG_FULLMASK, xi / lv[j], j);
+    if (lane == j) xi = xj;
+    else if (lane < j) xi = fma(-lv[j], xj, xi);
+  }
+  return xi;
+}
+
+__device__ __forceinline__ double warp_nmax_all(double v) {
+#pragma unroll
+  for (int o = 16; o; o >>= 1) v = nmax(v, __shfl_xor_sync(MG_FULLMASK, v, o));
+  return v;
+}
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+/* ----------------------------------------------------------- per-problem scratch */
+struct AdmmScr {
+  double* acl;   /* [T][NX*NX] Acl_t col-major: column i contiguous -> rows of Acl_t^T */
+  double* aclr;  /* [T][NX*NX] Acl_t row-major: row i contiguous */
+  double* rv;    /* [T][NX]    r_t */
+  double* tv;    /* [T][NX]    tmp_t = Vx_{t+1} + Vxx_fs_t */
+};
+
+/* ------------------------------------------------------ after a full Riccati sweep */
+/* Acl_t = Fx_t - Fu_t K_t in both orientations and b_t = fs_{t+1} - Fu_t k_t (stored in the
+ * dx~_{t+1} slot, the forward chain turns it into dx~_{t+1}); one warp per knot. */
+template <int NX, int NU>
+static __device__ __noinline__ void admm_post_full(const Prob& p, const AdmmScr& sc, double* sm, const AdmmSmem& s) {
+  extern __shared__ __align__(16) double sm_admm[];
+  sm = sm_admm;
+  using W = AdmmWs<NX, NU>;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  double* ws = sm + s.ws0 + warp * s.wsn;
+  for (int t = warp; t < p.T; t += nw) {
+    const double* Fx = p.Fx + (size_t)t * NX * NX;
+    const double* Fu = p.Fu + (size_t)t * NX * NU;
+    const double* K = p.K + (size_t)t * NX * NU;
+    double* A = sc.acl + (size_t)t * NX * NX;
+    double* AR = sc.aclr + (size_t)t * NX * NX;
+    /* lanes over rows i: Fu[i][.] in registers, K[.][j] broadcast */
+    for (int i0 = 0; i0 < NX; i0 += 32) {
+      const int i = i0 + lane;
+      const bool valid = i < NX;
+      const int ic = valid ? i : 0;
+      double fu[NU];
+#pragma unroll
+      for (int a = 0; a < NU; ++a) fu[a] = Fu[ic + NX * a];
+      for (int j = 0; j < NX; ++j) {
+        double acc = 0.0;
+#pragma unroll
+        for (int a = 0; a < NU; ++a) acc = fma(fu[a], K[a * NX + j], acc);
+        if (valid) A[i + NX * j] = Fx[i + NX * j] - acc;
+      }
+    }
+    /* lanes over columns j: K[.][j] in registers, Fu[i][.] broadcast; writes row i contiguously */
+    for (int j0 = 0; j0 < NX; j0 += 32) {
+      const int j = j0 + lane;
+      const bool valid = j < NX;
+      const int jc = valid ? j : 0;
+      double kk[NU];
+#pragma unroll
+      for (int a = 0; a < NU; ++a) kk[a] = K[a * NX + jc];
+      for (int i = 0; i < NX; ++i) {
+        double acc = 0.0;
+#pragma unroll
+        for (int a = 0; a < NU; ++a) acc = fma(Fu[i + NX * a], kk[a], acc);
+        if (valid) AR[i * NX + j] = Fx[i + NX * jc] - acc;
+      }
+    }
+    /* b_t */
+    for (int a = lane; a < NU; a += 32) ws[W::us + a] = p.kff[(size_t)t * NU + a];
+    __syncwarp();
+    waxpy<NX, NU>(Fu, ws + W::us, lane, [&](int i, double acc) {
+      p.dxt[(size_t)(t + 1) * NX + i] = p.fs[(size_t)(t + 1) * NX + i] - acc;
+    });
+    __syncwarp();
+  }
+}
+
+/* --------------------------------------------------------------------- the chains */
+/* BWD: Vx_t = r_t + Acl_t^T tmp_t, tmp_{t-1} = Vx_t + Vxx_fs_{t-1}, t = T-1 .. 0
+ * FWD: dx~_{t+1} = b_t + Acl_t dx~_t, t = 0 .. T-1
+ * Four lanes per output row, the warps holding threads < nchain take part (named barrier 1), each
+ * thread prefetches its slice of the next two knots' matrix through registers. */
+template <int NX, bool BWD>
+static __device__ __noinline__ void admm_chain(const Prob& p, const AdmmScr& sc, double* sm, const AdmmSmem& s, int nchain) {
+  extern __shared__ __align__(16) double sm_admm[];
+  sm = sm_admm;
+  const int tid = threadIdx.x;
+  if (tid >= nchain) return;
+  constexpr int KP = (NX + 7) / 8, PF = 2;
+  const int T = p.T, i = tid >> 2, q = tid & 3;
+  const bool valid = i < NX;
+  const int ic = valid ? i : 0;
+  const double* M = BWD ? sc.acl : sc.aclr;
+  double* vb = sm + s.vb;
+  double2 mreg[PF][KP];
+  double add0[PF], add1[PF];
+  auto knot_of = [&](int st) { return BWD ? T - 1 - st : st; };
+  auto load = [&](auto SLOT, int st) {
+    constexpr int sl = decltype(SLOT)::value;
+    const int t = knot_of(st);
+    const double* row = M + (size_t)t * NX * NX + (size_t)ic * NX;
+#pragma unroll
+    for (int m = 0; m < KP; ++m) {
+      const int k = 2 * q + 8 * m;
+      mreg[sl][m] = (k < NX) ? *reinterpret_cast<const double2*>(row + k) : make_double2(0.0, 0.0);
+    }
+    add0[sl] = 0.0; add1[sl] = 0.0;
+    if (q == 0) {
+      if (BWD) {
+        add0[sl] = sc.rv[(size_t)t * NX + ic];
+        add1[sl] = t > 0 ? p.Vxx_fs[(size_t)(t - 1) * NX + ic] : 0.0;
+      } else {
+        add0[sl] = p.dxt[(size_t)(t + 1) * NX + ic];
+      }
+    }
+  };
+  if (tid < NX) vb[tid] = BWD ? sc.tv[(size_t)(T - 1) * NX + tid] : p.dxt[tid];
+  load(std::integral_constant<int, 0>{}, 0);
+  if (T > 1) load(std::integral_constant<int, 1>{}, 1);
+  named_bar_sync(1, nchain);
+  auto step = [&](auto SLOT, int st) {
+    constexpr int sl = decltype(SLOT)::value;
+    const int t = knot_of(st);
+    const double* v = vb + (st & 1) * NX;
+    double* vn = vb + ((st + 1) & 1) * NX;
+    double a0 = 0.0, a1 = 0.0;
+#pragma unroll
+    for (int m = 0; m < KP; ++m) {
+      const int k = 2 * q + 8 * m;
+      if (k < NX) {
+        const double2 vv = *reinterpret_cast<const double2*>(v + k);
+        a0 = fma(mreg[sl][m].x, vv.x, a0);
+        a1 = fma(mreg[sl][m].y, vv.y, a1);
+      }
+    }
+    double acc = a0 + a1;
+    acc += __shfl_xor_sync(MG_FULLMASK, acc, 1);
+    acc += __shfl_xor_sync(MG_FULLMASK, acc, 2);
+    const double c0 = add0[sl], c1 = add1[sl];
+    if (st + PF < T) load(SLOT, st + PF);
+    if (valid && q == 0) {
+      if (BWD) {
+        const double vx = c0 + acc;
+        p.Vx[(size_t)t * NX + i] = vx;
+        if (t > 0) {
+          const double tn = vx + c1;
+          sc.tv[(size_t)(t - 1) * NX + i] = tn;
+          vn[i] = tn;
+        }
+      } else {
+        const double xn = c0 + acc;
+        p.dxt[(size_t)(t + 1) * NX + i] = xn;
+        vn[i] = xn;
+      }
+    }
+    named_bar_sync(1, nchain);
+  };
+  for (int st = 0; st < T; st += PF) {
+    step(std::integral_constant<int, 0>{}, st);
+    if (st + 1 < T) step(std::integral_constant<int, 1>{}, st + 1);
+  }
+}
+
+/* --------------------------------------------- gains and b_t after the backward chain */
+/* Qu_t = qu_t + Fu_t^T tmp_t, k_t = Quu_t^-1 Qu_t (src/csqp.cpp:1083-1097), b_t = fs_{t+1} - Fu_t k_t;
+ * one warp per knot.  qu_t was left in the Qu_ slot by admm_update. */
+template <int NX, int NU>
+static __device__ __noinline__ void admm_gains(const Prob& p, const AdmmScr& sc, double* sm, const AdmmSmem& s) {
+  extern __shared__ __align__(16) double sm_admm[];
+  sm = sm_admm;
+  using W = AdmmWs<NX, NU>;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  double* ws = sm + s.ws0 + warp * s.wsn;
+  double *xs = ws + W::xs, *us = ws + W::us, *qu = ws + W::qu;
+  for (int t = warp; t < p.T; t += nw) {
+    const double* Fu = p.Fu + (size_t)t * NX * NU;
+    for (int i = lane; i < NX; i += 32) xs[i] = sc.tv[(size_t)t * NX + i];
+    __syncwarp();
+    wdot4<NX>(Fu, NU, xs, lane, [&](int a, double acc) {
+      double v = p.Qu[(size_t)t * NU + a];
+      v += acc;
+      qu[a] = v;
+      p.Qu[(size_t)t * NU + a] = v;
+    });
+    __syncwarp();
+    double ki = (lane < NU) ? qu[lane] : 0.0;
+    ki = wsolve_llt<NU>(p.L + (size_t)t * NU * NU, ki, lane);
+    if (lane < NU) { us[lane] = ki; p.kff[(size_t)t * NU + lane] = ki; }
+    __syncwarp();
+    waxpy<NX, NU>(Fu, us, lane, [&](int i, double acc) {
+      p.dxt[(size_t)(t + 1) * NX + i] = p.fs[(size_t)(t + 1) * NX + i] - acc;
+    });
+    __syncwarp();
+  }
+}
+
+/* ------------------------------- du~, update_lagrangian_parameters, r_t of the next sweep */
+/* One knot: du~_t = -k_t - K_t dx~_t (src/csqp.cpp:636-637); dx_ := dx~, du_ := du~ (:1222-1226,
+ * 1241-1242); c = Gx dx~ + Gu du~, z_relaxed, z, y (:1229-1239); the residual norms on check
+ * iterations (:1244-1278); and, when the next backward sweep is a light one, its knot-local terms
+ * qu_t (left in the Qu_ slot) and r_t = qx_t - K_t^T qu_t (src/csqp.cpp:1068-1104 regrouped). */
+template <int NX, int NU>
+static __device__ __noinline__ void admm_update(const Prob& p, const AdmmScr& sc, double* sm, const AdmmSmem& s,
+                                                const mimgpu_csqp_params& q_, int iter, bool need_r, AdmmNorms& n) {
+  extern __shared__ __align__(16) double sm_admm[];
+  sm = sm_admm;
+  using W = AdmmWs<NX, NU>;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  const int T = p.T, ng = p.ng, ngT = p.ngT;
+  const int ngm = ng > ngT ? ng : ngT;
+  double* ws = sm + s.ws0 + warp * s.wsn;
+  double *xs = ws + W::xs, *us = ws + W::us, *sqx = ws + W::qx, *squ = ws + W::qu, *sd = ws + W::ds, *se1 = sd + ngm,
+         *se2 = se1 + ngm;
+  const bool check = (iter % q_.rho_update_interval) == 0;
+  const bool heur = q_.update_rho_with_heuristic != 0;
+  const bool dualg = check && !heur;
+  const double alpha = q_.alpha, sigma = q_.sigma;
+  double np_ = -CUDART_INF, nd_ = -CUDART_INF, npr = -CUDART_INF, ndr = -CUDART_INF; /* src/csqp.cpp:1201-1204 */
+
+  /* rows r of one knot: c given, z / y projection and the row-local norms; returns d_r */
+  auto project = [&](size_t o, int r, double c, const double* g, const double* lb, const double* ub) {
+    const double zp = p.z[o + r];
+    double zr = alpha * c;
+    zr += (1. - alpha) * zp;
+    const double rho = p.rho[o + r], irho = 1. / rho, yo = p.y[o + r];
+    double z = zr + yo * irho;
+    const double lo = lb[r] - g[r], hi = ub[r] - g[r];
+    z = (z < lo) ? lo : z;
+    z = (hi < z) ? hi : z;
+    const double yn = yo + rho * (zr - z);
+    p.z[o + r] = z;
+    p.y[o + r] = yn;
+    double d = yn;
+    d -= rho * z;
+    sd[r] = d;
+    if (check) {
+      se1[r] = rho * (z - zp); se2[r] = yn;
+      np_ = nmax(np_, fabs(c - z));
+      npr = nmax(npr, fabs(c));
+      npr = nmax(npr, fabs(z));
+      if (heur) {
+        nd_ = nmax(nd_, fabs(rho * (z - zp)));
+        ndr = nmax(ndr, fabs(yn));
+      }
+    }
+  };
+
+  for (int t = warp; t <= T; t += nw) {
+    const bool last = (t == T);
+    const int nc = last ? ngT : ng;
+    for (int i = lane; i < NX; i += 32) {
+      const double x = p.dxt[(size_t)t * NX + i];
+      xs[i] = x;
+      p.dx[(size_t)t * NX + i] = x;
+    }
+    __syncwarp();
+    if (!last) {
+      const double* K = p.K + (size_t)t * NX * NU;
+      wdot4<NX>(K, NU, xs, lane, [&](int a, double acc) {
+        double u = -p.kff[(size_t)t * NU + a];
+        u -= acc;
+        us[a] = u;
+        p.dut[(size_t)t * NU + a] = u;
+        p.du[(size_t)t * NU + a] = u;
+      });
+      __syncwarp();
+    }
+    const double* Gx = last ? p.GxT : (ng ? p.Gx + (size_t)t * ng * NX : nullptr);
+    const double* Gu = (last || !ng) ? nullptr : p.Gu + (size_t)t * ng * NU;
+    const size_t o = (size_t)t * ng;
+    if (nc) {
+      /* c_r = sum_j Gx[r][j] dx~[j] + sum_a Gu[r][a] du~[a]: lanes over rows, columns split over lane groups */
+      const int np2 = nc <= 4 ? 4 : nc <= 8 ? 8 : nc <= 16 ? 16 : 32, ph_n = 32 / np2;
+      const int rl = lane % np2, ph = lane / np2;
+      const double* g = last ? p.gT : p.g + o;
+      const double* lb = last ? p.glbT : p.glb + o;
+      const double* ub = last ? p.gubT : p.gub + o;
+      for (int r0 = 0; r0 < nc; r0 += np2) {
+        const int r = r0 + rl;
+        const bool valid = r < nc;
+        const int rc = valid ? r : 0;
+        double a1 = 0.0, a2 = 0.0;
+        for (int j = ph; j < NX; j += ph_n) a1 = fma(Gx[rc + nc * j], xs[j], a1);
+        if (Gu)
+          for (int a = ph; a < NU; a += ph_n) a2 = fma(Gu[rc + nc * a], us[a], a2);
+        for (int off = np2; off < 32; off <<= 1) {
+          a1 += __shfl_xor_sync(MG_FULLMASK, a1, off);
+          a2 += __shfl_xor_sync(MG_FULLMASK, a2, off);
+        }
+        if (valid && ph == 0) {
+          double c = 0.0;
+          c += a1;
+          c += a2;
+          project(o, r, c, g, lb, ub);
+        }
+      }
+      __syncwarp();
+    }
+    /* knot-local terms of the next light backward sweep, and the G^T products of the dual norms */
+    if (last) {
+      if (need_r || (dualg && nc)) {
+        /* column i of GxT (ngT contiguous) against d, rho dz, y */
+        wdot4_rt3(p.GxT, NX, nc, (need_r && nc) ? sd : nullptr, (dualg && nc) ? se1 : nullptr,
+                  (dualg && nc) ? se2 : nullptr, lane, [&](int i, double s0, double s1, double s2) {
+                    if (dualg && nc) { nd_ = nmax(nd_, fabs(s1)); ndr = nmax(ndr, fabs(s2)); }
+                    if (need_r) { /* Vx_T (src/csqp.cpp:1045-1052) and tmp_{T-1} */
+                      double v = p.LxT[i];
+                      v -= sigma * xs[i];
+                      if (nc) v += s0;
+                      p.Vx[(size_t)T * NX + i] = v;
+                      sc.tv[(size_t)(T - 1) * NX + i] = v + p.Vxx_fs[(size_t)(T - 1) * NX + i];
+                    }
+                  });
+      }
+      __syncwarp();
+      continue;
+    }
+    if (need_r || (dualg && nc)) {
+      const bool gx_d = need_r && nc && t > 0;   /* x0 is fixed: no Gx^T d at t = 0 (src/csqp.cpp:1073) */
+      if (nc) {
+        wdot4_rt3(Gx, NX, nc, gx_d ? sd : nullptr, dualg ? se1 : nullptr, dualg ? se2 : nullptr, lane,
+                  [&](int i, double s0, double s1, double s2) {
+                    if (dualg) { nd_ = nmax(nd_, fabs(s1)); ndr = nmax(ndr, fabs(s2)); }
+                    if (need_r) {
+                      double v = p.Lx[(size_t)t * NX + i];
+                      v -= sigma * xs[i];
+                      if (gx_d) v += s0;
+                      sqx[i] = v;
+                    }
+                  });
+        wdot4_rt3(Gu, NU, nc, need_r ? sd : nullptr, dualg ? se1 : nullptr, dualg ? se2 : nullptr, lane,
+                  [&](int a, double s0, double s1, double s2) {
+                    if (dualg) { nd_ = nmax(nd_, fabs(s1)); ndr = nmax(ndr, fabs(s2)); }
+                    if (need_r) {
+                      double v = p.Lu[(size_t)t * NU + a];
+                      v -= sigma * us[a];
+                      v += s0;
+                      squ[a] = v;
+                      p.Qu[(size_t)t * NU + a] = v;
+                    }
+                  });
+      } else if (need_r) {
+        for (int i = lane; i < NX; i += 32) sqx[i] = p.Lx[(size_t)t * NX + i] - sigma * xs[i];
+        for (int a = lane; a < NU; a += 32) {
+          const double v = p.Lu[(size_t)t * NU + a] - sigma * us[a];
+          squ[a] = v;
+          p.Qu[(size_t)t * NU + a] = v;
+        }
+      }
+      __syncwarp();
+      if (need_r) { /* r_t = qx_t - K_t^T qu_t; K row-major NU x NX = col-major NX x NU */
+        waxpy<NX, NU>(p.K + (size_t)t * NX * NU, squ, lane,
+                      [&](int i, double acc) { sc.rv[(size_t)t * NX + i] = sqx[i] - acc; });
+      }
+      __syncwarp();
+    }
+  }
+  /* src/csqp.cpp:1201-1204: the four norms are -inf unless this is a check iteration */
+  n.primal = n.dual = n.primal_rel = n.dual_rel = -CUDART_INF;
+  if (check) {
+    double* red = sm + s.red;
+    np_ = warp_nmax_all(np_); nd_ = warp_nmax_all(nd_); npr = warp_nmax_all(npr); ndr = warp_nmax_all(ndr);
+    __syncthreads();
+    if (lane == 0) { red[warp] = np_; red[16 + warp] = nd_; red[32 + warp] = npr; red[48 + warp] = ndr; }
+    __syncthreads();
+    for (int w = 0; w < nw; ++w) {
+      n.primal = nmax(n.primal, red[w]); n.dual = nmax(n.dual, red[16 + w]);
+      n.primal_rel = nmax(n.primal_rel, red[32 + w]); n.dual_rel = nmax(n.dual_rel, red[48 + w]);
+    }
+  }
+  __syncthreads();
+}
+
+/* ------------------------------------------------------------------ the kernel */
+struct AdmmKPar {
+  mimgpu_csqp_params q;
+  int with_kkt, ric_total, nchain, dbg;
+  double *acl, *aclr, *rv, *tv; /* [B][T][...] scratch of the condensed iterations */
+};
+
+template <int NX, int NU> struct AdmmTune { static constexpr int MAXT = NX <= 16 ? 128 : 256, MINB = NX <= 16 ? 6 : 2; };
+template <> struct AdmmTune<36, 12> { static constexpr int MAXT = 192, MINB = 2; };
+template <> struct AdmmTune<12, 6> { static constexpr int MAXT = 96, MINB = 8; };
+template <> struct AdmmTune<32, 16> { static constexpr int MAXT = 192, MINB = 2; };
+template <> struct AdmmTune<64, 32> { static constexpr int MAXT = 384, MINB = 1; };
+template <> struct AdmmTune<76, 32> { static constexpr int MAXT = 384, MINB = 1; };
+template <> struct AdmmTune<48, 24> { static constexpr int MAXT = 256, MINB = 1; };
+
+template <int MODE>
+static __device__ __noinline__ int admm_riccati_generic(const Prob& p, double* sm, const Smem& s, const RicPar& rp,
+                                                        int stage_fx) {
+  return riccati_backward<MODE>(p, as_shared(sm), s, rp, stage_fx);
+}
+static __device__ __noinline__ void admm_forward_eq(const Prob& p, double* sm, const Smem& s) { csqp_forward_eq(p, as_shared(sm), s); }
+static __device__ __noinline__ void admm_kkt(const Prob& p, double* sm, const Smem& s) { csqp_kkt(p, as_shared(sm), s); }
+
+/* SolverCSQP::computeDirection (src/csqp.cpp:454-517): control flow of csqp_direction_body
+ * (kernels_generic.cuh); USE_MMA selects the DMMA Riccati sweep for the full iterations. */
+template <int NX, int NU, bool USE_MMA>
+__global__ void __launch_bounds__(AdmmTune<NX, NU>::MAXT, AdmmTune<NX, NU>::MINB)
+k_csqp_direction_admm(KArgs a, AdmmKPar kp) {
+  static_assert(NX % 2 == 0 && NU % 2 == 0 && NU <= 32, "16-byte rows, one lane per control in the gain solve");
+  extern __shared__ __align__(16) double sm_admm[];
+  if ((int)blockIdx.x >= a.n_active) return;
+  const int b = a.active ? a.active[blockIdx.x] : (int)blockIdx.x;
+  Prob p = bind(a, b);
+  const int nw = blockDim.x >> 5;
+  const AdmmSmem ss = admm_layout<NX, NU>(p.ng, p.ngT, nw, kp.ric_total);
+  double* sm = sm_admm;
+  double* gsm = sm + ss.uni; /* Riccati layouts live in the union region */
+  const Smem gs = smem_layout(NX, NU, p.ng, p.ngT, a.stage_fx);
+  RicSmem rs{};
+  if constexpr (USE_MMA) rs = ric_layout<NX, NU>(p.ng, p.ngT, true);
+  uint64_t* ric_bars = reinterpret_cast<uint64_t*>(sm + ss.bars);
+  uint32_t ric_seq = 0u;
+  if (threadIdx.x == 0) {
+    mbar_init(ric_bars, 1);
+    mbar_init(ric_bars + 1, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  AdmmScr sc;
+  {
+    const size_t sb = (size_t)b * p.T;
+    sc.acl = kp.acl + sb * NX * NX; sc.aclr = kp.aclr + sb * NX * NX;
+    sc.rv = kp.rv + sb * NX; sc.tv = kp.tv + sb * NX;
+  }
+  const mimgpu_csqp_params& q = kp.q;
+  const size_t B = p.B;
+  const int nc = p.T * p.ng + p.ngT;
+  double rho_sparse = p.scal[MIMGPU_S_RHO_SPARSE * B + b];
+  RicPar rp;
+  rp.preg = a.preg_arr ? a.preg_arr[b] : q.preg;
+  rp.dreg = a.dreg_arr ? a.dreg_arr[b] : q.dreg;
+  rp.sigma = q.sigma;
+  rp.is_feasible = 0;
+  /* reset_params (src/csqp.cpp:170-193) */
+  if (q.reset_rho) { rho_sparse = q.rho_sparse_base; csqp_apply_rho(p, rho_sparse, q.rho_min); }
+  for (int e = threadIdx.x; e < nc; e += blockDim.x) { p.z[e] = 0.0; if (q.reset_y) p.y[e] = 0.0; }
+  __syncthreads();
+  int st = 0, converged = 0, it = 0;
+  AdmmNorms n;
+  n.primal = p.scal[MIMGPU_S_NORM_PRIMAL * B + b]; n.dual = p.scal[MIMGPU_S_NORM_DUAL * B + b];
+  n.primal_rel = p.scal[MIMGPU_S_NORM_PRIMAL_REL * B + b]; n.dual_rel = p.scal[MIMGPU_S_NORM_DUAL_REL * B + b];
+  if (q.equality_qp_initial_guess) { /* src/csqp.cpp:461-464 */
+    if constexpr (USE_MMA) st = ric_backward_mma<MODE_FULL, NX, NU>(p, gsm, rs, rp, ric_bars, ric_seq, true);
+    else st = admm_riccati_generic<MODE_EQ>(p, gsm, gs, rp, a.stage_fx);
+    if (!st) { __syncthreads(); admm_forward_eq(p, gsm, gs); }
+  }
+  const int interval = q.rho_update_interval;
+  auto is_full = [&](int k) { return k % interval == 1 || interval == 1; };
+  if (!st) {
+    for (it = 1; it < q.max_qp_iters + 1; ++it) { /* src/csqp.cpp:470 */
+      if (is_full(it)) {
+        if constexpr (USE_MMA) st = ric_backward_mma<MODE_FULL, NX, NU>(p, gsm, rs, rp, ric_bars, ric_seq);
+        else st = admm_riccati_generic<MODE_FULL>(p, gsm, gs, rp, a.stage_fx);
+        if (st) break;
+        __syncthreads();
+        admm_post_full<NX, NU>(p, sc, sm, ss);
+      } else {
+        admm_chain<NX, true>(p, sc, sm, ss, kp.nchain);
+        __syncthreads();
+        admm_gains<NX, NU>(p, sc, sm, ss);
+      }
+      __syncthreads();
+      admm_chain<NX, false>(p, sc, sm, ss, kp.nchain);
+      __syncthreads();
+      const bool need_r = (it + 1 < q.max_qp_iters + 1) && !is_full(it + 1);
+      admm_update<NX, NU>(p, sc, sm, ss, q, it, need_r, n);
+      if (it % interval == 0) {
+        /* update_rho_vec (src/csqp.cpp:519-532) */
+        const double scale = sqrt((n.primal * n.dual_rel) / (n.dual * n.primal_rel));
+        const double rho_est = std_min(std_max(scale * rho_sparse, q.rho_min), q.rho_max);
+        if (rho_est > rho_sparse * q.adaptive_rho_tolerance || rho_est < rho_sparse / q.adaptive_rho_tolerance) {
+          rho_sparse = rho_est;
+          csqp_apply_rho(p, rho_sparse, q.rho_min);
+          __syncthreads();
+        }
+        double tol_p, tol_d; /* src/csqp.cpp:497-512 */
+        if (fabs(q.eps_rel) <= 2.220446049250313e-16) {
+          tol_p = q.eps_abs; tol_d = q.eps_abs;
+        } else {
+          tol_p = q.eps_abs + q.eps_rel * n.primal_rel;
+          tol_d = q.eps_abs + q.eps_rel * n.dual_rel;
+        }
+        if (n.primal <= tol_p && n.dual <= tol_d) { converged = 1; break; }
+      }
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    a.status[b] = st; a.qp_iters[b] = it; a.converged[b] = converged;
+    p.scal[MIMGPU_S_RHO_SPARSE * B + b] = rho_sparse;
+    p.scal[MIMGPU_S_NORM_PRIMAL * B + b] = n.primal; p.scal[MIMGPU_S_NORM_DUAL * B + b] = n.dual;
+    p.scal[MIMGPU_S_NORM_PRIMAL_REL * B + b] = n.primal_rel; p.scal[MIMGPU_S_NORM_DUAL_REL * B + b] = n.dual_rel;
+  }
+  if (!st && kp.with_kkt) admm_kkt(p, gsm, gs);
+}
+
+/* ------------------------------------------------------------------- dispatch */
+/* shapes with a DMMA Riccati sweep for the full iterations | shapes whose full iterations run the
+ * shape-generic sweep (constrained DMMA layout does not fit 227 KB, or NX % 4 != 0) */
+#define MIMGPU_ADMM_MMA_SHAPES(X) X(12, 6) X(36, 12) X(16, 8) X(8, 4) X(32, 16) X(4, 2)
+#define MIMGPU_ADMM_GEN_SHAPES(X) X(6, 2) X(10, 4) X(64, 32) X(76, 32) X(48, 24) X(24, 12)
+
+template <int NX, int NU, bool MMA>
+static AdmmPlan admm_plan_t(const mimgpu_shape& sh, int stage_fx, int max_smem) {
+  AdmmPlan pl{};
+  const Smem gs = smem_layout(NX, NU, sh.ng, sh.ngT, stage_fx);
+  pl.nt = AdmmTune<NX, NU>::MAXT;
+  pl.nchain = ((4 * NX + 31) / 32) * 32;
+  if (pl.nchain > pl.nt) return pl;
+  for (int mma = MMA ? 1 : 0; mma >= 0; --mma) {
+    int ric_total = gs.total;
+    if (mma) {
+      if constexpr (MMA) {
+        const RicSmem rs = ric_layout<NX, NU>(sh.ng, sh.ngT, true);
+        if (rs.total > ric_total) ric_total = rs.total;
+      }
+    }
+    const AdmmSmem ss = admm_layout<NX, NU>(sh.ng, sh.ngT, pl.nt / 32, ric_total);
+    const int bytes = ss.total * 8;
+    if (bytes > max_smem) continue;
+    cudaError_t e;
+    if (mma) {
+      if constexpr (MMA) e = cudaFuncSetAttribute(k_csqp_direction_admm<NX, NU, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+      else e = cudaErrorInvalidValue;
+    } else {
+      e = cudaFuncSetAttribute(k_csqp_direction_admm<NX, NU, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    }
+    if (e != cudaSuccess) { cudaGetLastError(); continue; }
+    pl.ok = 1; pl.use_mma = mma; pl.ric_total = ric_total; pl.smem_bytes = bytes;
+    return pl;
+  }
+  return pl;
+}
+
+static inline AdmmPlan admm_plan(const mimgpu_shape& sh, int stage_fx, int max_smem) {
+#define X(NX_, NU_) \
+  if (sh.nx == NX_ && sh.nu == NU_) return admm_plan_t<NX_, NU_, true>(sh, stage_fx, max_smem);
+  MIMGPU_ADMM_MMA_SHAPES(X)
+#undef X
+#define X(NX_, NU_) \
+  if (sh.nx == NX_ && sh.nu == NU_) return admm_plan_t<NX_, NU_, false>(sh, stage_fx, max_smem);
+  MIMGPU_ADMM_GEN_SHAPES(X)
+#undef X
+  return AdmmPlan{};
+}
+
+static inline int admm_csqp_launch(const KArgs& a, const mimgpu_csqp_params& q, int with_kkt, const AdmmPlan& pl,
+                                   double* const scratch[4], cudaStream_t st) {
+  AdmmKPar kp;
+  kp.q = q; kp.with_kkt = with_kkt; kp.ric_total = pl.ric_total; kp.nchain = pl.nchain; kp.dbg = 0;
+  kp.acl = scratch[0]; kp.aclr = scratch[1]; kp.rv = scratch[2]; kp.tv = scratch[3];
+#define X(NX_, NU_)                                                                                         \
+  if (a.sh.nx == NX_ && a.sh.nu == NU_) {                                                                   \
+    if (pl.use_mma) k_csqp_direction_admm<NX_, NU_, true><<<a.n_active, pl.nt, pl.smem_bytes, st>>>(a, kp); \
+    else k_csqp_direction_admm<NX_, NU_, false><<<a.n_active, pl.nt, pl.smem_bytes, st>>>(a, kp);           \
+    return 0;                                                                                               \
+  }
+  MIMGPU_ADMM_MMA_SHAPES(X)
+#undef X
+#define X(NX_, NU_)                                                                                         \
+  if (a.sh.nx == NX_ && a.sh.nu == NU_) {                                                                   \
+    k_csqp_direction_admm<NX_, NU_, false><<<a.n_active, pl.nt, pl.smem_bytes, st>>>(a, kp);                \
+    return 0;                                                                                               \
+  }
+  MIMGPU_ADMM_GEN_SHAPES(X)
+#undef X
+  return -1;
+}
+
+}  // namespace mimgpu

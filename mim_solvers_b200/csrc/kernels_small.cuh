@@ -533,7 +533,7 @@ __global__ void __launch_bounds__(WPB * 32, GjTune<NX, NU>::MINB) k_sqp_directio
   if (lane == 0) { a.status[b] = st; a.qp_iters[b] = 0; }
   if (st) {
     double gap = 0.0;
-    for (int e = lane; e < (T + 1) * NX; e += 32) gap += fabs(p.fs[e]);
+    for (int e = lane; e < (T + 1) * NX; e += 32) gap += fabs(pk[(size_t)(e / NX) * C::REC + C::bFs + e % NX]); /* fs_t heads every record */
     gap = warp_sum(gap);
     if (lane == 0) {
       p.scal[MIMGPU_S_GAP_NORM * (size_t)p.B + b] = gap;
@@ -571,6 +571,37 @@ __global__ void __launch_bounds__(128) k_pack_knots(KArgs a, double* pack, int b
   copy(dst + C::bF, a.Fx + k * NX * NX, NX * NX);
   copy(dst + C::bF + NX * NX, a.Fu + k * NX * NU, NX * NU);
   (void)N;
+}
+
+/* Inverse of k_pack_knots: knot records -> the field-major C-ABI arrays (out.Fx ... are written).
+ * Needed only when a caller that uploaded RECORDS later asks for something the record kernel does
+ * not serve (Qu_/Quuk_/Quu_llt_ downloads, FDDP or CSQP on the same ctx). */
+struct UnpackDst {
+  double *Fx, *Fu, *Lxx, *Lxu, *Luu, *Lx, *Lu, *fs, *LxxT, *LxT;
+};
+template <int NX, int NU>
+__global__ void __launch_bounds__(128) k_unpack_records(const double* pack, UnpackDst o, int T) {
+  using C = GjCfg<NX, NU>;
+  const size_t b = blockIdx.x / (T + 1);
+  const int t = blockIdx.x % (T + 1);
+  const double* src = pack + b * C::pack_doubles(T) + (size_t)t * C::REC;
+  auto copy = [&](double* d, const double* s, int n) {
+    for (int e = threadIdx.x; e < n; e += blockDim.x) d[e] = s[e];
+  };
+  copy(o.fs + (b * (T + 1) + t) * NX, src + C::bFs, NX);
+  if (t == T) {
+    copy(o.LxxT + b * NX * NX, src + C::tLxx, NX * NX);
+    copy(o.LxT + b * NX, src + C::tLx, NX);
+    return;
+  }
+  const size_t k = b * T + t;
+  copy(o.Lxx + k * NX * NX, src + C::bH, NX * NX);
+  copy(o.Lxu + k * NX * NU, src + C::bH + NX * NX, NX * NU);
+  copy(o.Luu + k * NU * NU, src + C::bLuu, NU * NU);
+  copy(o.Lx + k * NX, src + C::bL, NX);
+  copy(o.Lu + k * NU, src + C::bL + NX, NU);
+  copy(o.Fx + k * NX * NX, src + C::bF, NX * NX);
+  copy(o.Fu + k * NX * NU, src + C::bF + NX * NX, NX * NU);
 }
 
 /* On-demand copy of the spill records into the solver-member arrays Vxx_ Vx_ K_ k_ of the C ABI. */
@@ -700,6 +731,40 @@ static inline int small_pack_launch(const KArgs& a, double* pack, int b0, int nb
       return 0;                                                                                 \
     }                                                                                           \
     return -1;                                                                                  \
+  }
+  MIMGPU_SMALL_SHAPES(X)
+#undef X
+  return -1;
+}
+/* knot records -> field-major arrays (a.Fx ... must point at writable storage), all B problems */
+static inline int small_unpack_inputs_launch(const KArgs& a, const double* pack, cudaStream_t st) {
+  UnpackDst o{const_cast<double*>(a.Fx), const_cast<double*>(a.Fu), const_cast<double*>(a.Lxx), const_cast<double*>(a.Lxu),
+              const_cast<double*>(a.Luu), const_cast<double*>(a.Lx), const_cast<double*>(a.Lu), const_cast<double*>(a.fs),
+              const_cast<double*>(a.LxxT), const_cast<double*>(a.LxT)};
+#define X(NX_, NU_)                                                                                   \
+  if (a.sh.nx == NX_ && a.sh.nu == NU_) {                                                             \
+    if constexpr (NX_ % 4 == 0) {                                                                     \
+      k_unpack_records<NX_, NU_><<<(unsigned)a.sh.B * (a.sh.T + 1), 128, 0, st>>>(pack, o, a.sh.T);   \
+      return 0;                                                                                       \
+    }                                                                                                 \
+    return -1;                                                                                        \
+  }
+  MIMGPU_SMALL_SHAPES(X)
+#undef X
+  return -1;
+}
+/* offsets (in doubles) of every block inside a knot record / the terminal record */
+static inline int small_record_offsets(const mimgpu_shape& s, int out[16]) {
+#define X(NX_, NU_)                                                                                   \
+  if (s.nx == NX_ && s.nu == NU_) {                                                                   \
+    if constexpr (NX_ % 4 == 0) {                                                                     \
+      using C = GjCfg<NX_, NU_>;                                                                      \
+      const int v[16] = {C::REC, C::TREC, (int)C::pack_doubles(s.T), C::bFs, C::bH, C::bH + NX_ * NX_, C::bLuu, C::bL, \
+                         C::bL + NX_, C::bF, C::bF + NX_ * NX_, C::tFs, C::tLxx, C::tLx, 0, 0};      \
+      for (int i = 0; i < 16; ++i) out[i] = v[i];                                                     \
+      return 0;                                                                                       \
+    }                                                                                                 \
+    return -1;                                                                                        \
   }
   MIMGPU_SMALL_SHAPES(X)
 #undef X

@@ -61,6 +61,20 @@ struct mimgpu_ctx {
   SqpKPar last_sqp{};              /* its parameters, for the on-demand recomputation */
   CtaPlan cplan{};                 /* DMMA CTA-per-problem SQP / FDDP kernel (kernels_cta.cuh) */
   StreamPlan splan{};              /* streaming CSQP kernel (kernels_stream.cuh), ok = 0: not available */
+  AdmmPlan aplan{};                /* condensed-chain CSQP kernel (kernels_admm.cuh): the default CSQP path */
+  double* admm_scr[4] = {nullptr, nullptr, nullptr, nullptr}; /* Acl, Acl row-major, r, tmp: allocated at the first CSQP call */
+  /* debug / A-B switches, read ONCE at mimgpu_create (never on the hot path) */
+  bool force_generic = false;      /* MIMGPU_FORCE_GENERIC: shape-generic kernels only */
+  bool csqp_stream = false;        /* MIMGPU_CSQP_STREAM: round-1 streaming CSQP kernel instead of the condensed one */
+  bool small_alt = false;          /* MIMGPU_SMALL_FULL / MIMGPU_SMALL_NOMMA: full-spill small kernel as default */
+  bool warned_generic = false;
+  int last_kind = 0;               /* 0 none, 1 SQP, 2 FDDP, 3 CSQP: what the last direction call was */
+  bool pack_dirty = false;         /* field-major inputs changed since the knot records were built */
+  bool attached = false;           /* inputs are caller-owned device memory: re-read at EVERY direction call */
+  bool records_mode = false;       /* inputs arrived as knot records (mimgpu_upload_records) */
+  bool fields_valid = true;        /* records mode: the field-major arrays have been rebuilt from the records */
+  double* cost_buf = nullptr;      /* [B] cost_ of host-side record uploads */
+  cudaStream_t last_stream = nullptr; /* stream of the last asynchronous call (ordering of the chunked host path) */
 };
 
 static size_t deriv_sizes(const mimgpu_shape& s, size_t n[20]) {
@@ -231,7 +245,11 @@ static int configure_launch(mimgpu_ctx* c) {
   CU(cudaFuncSetAttribute(k_csqp_direction_generic, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
   c->use_small = small_kernels_configure_x(s);
   c->splan = stream_plan_x(s, stage, max_smem);
+  c->aplan = admm_plan_x(s, stage, max_smem);
   c->cplan = cta_plan_x(s, stage, max_smem);
+  c->force_generic = getenv("MIMGPU_FORCE_GENERIC") != nullptr;
+  c->csqp_stream = getenv("MIMGPU_CSQP_STREAM") != nullptr;
+  c->small_alt = getenv("MIMGPU_SMALL_FULL") != nullptr || getenv("MIMGPU_SMALL_NOMMA") != nullptr;
   return MIMGPU_OK;
 }
 
@@ -282,6 +300,7 @@ int mimgpu_create(mimgpu_ctx** out, int device, const mimgpu_shape* shape) {
   if (e == cudaSuccess) e = cudaMemset(c->ibuf, 0, sizeof(int32_t) * 4 * (size_t)s.B);
   if (e == cudaSuccess) e = cudaMalloc(&c->reg_buf, sizeof(double) * 2 * (size_t)s.B);
   if (e == cudaSuccess) e = cudaMalloc(&c->summary_dev, sizeof(SummaryDev));
+  if (e == cudaSuccess) e = cudaMalloc(&c->cost_buf, sizeof(double) * (size_t)s.B);
   if (e == cudaSuccess && (c->use_small & 2) &&
       small_pack_layout_x(s, &c->pack_pp, &c->spill_pp) == 0) {
     e = cudaMalloc(&c->pack_buf, c->pack_pp * (size_t)s.B * sizeof(double));
@@ -306,6 +325,8 @@ void mimgpu_destroy(mimgpu_ctx* c) {
   cudaSetDevice(c->device);
   if (c->pipe_st[0]) cudaStreamDestroy(c->pipe_st[0]);
   if (c->pipe_st[1]) cudaStreamDestroy(c->pipe_st[1]);
+  for (int i = 0; i < 4; ++i) cudaFree(c->admm_scr[i]);
+  cudaFree(c->cost_buf);
   cudaFree(c->pack_buf); cudaFree(c->spill_buf); cudaFree(c->in_buf); cudaFree(c->state_buf); cudaFree(c->ibuf); cudaFree(c->reg_buf); cudaFree(c->summary_dev);
   delete c;
 }
@@ -317,18 +338,55 @@ int mimgpu_get_shape(const mimgpu_ctx* c, mimgpu_shape* shape) {
 }
 
 /* ------------------------------------------------------------------ data in */
-/* Shapes served by the fast warp-per-problem SQP kernel keep a second, knot-packed copy of the
- * inputs (one record per knot, kernels_small_gj.cuh): built here, right after the upload, by one
- * streaming pass on the device (read + write of the inputs at HBM speed). */
+/* Shapes served by the fast warp-per-problem SQP kernel read KNOT RECORDS (one record per knot,
+ * kernels_small_gj.cuh).  A caller can hand the records in directly (mimgpu_upload_records: no
+ * re-layout at all); field-major inputs are re-laid-out by one streaming pass (k_pack_knots, read +
+ * write of the inputs at HBM speed) as part of the direction call that consumes them. */
 static int pack_inputs(mimgpu_ctx* c, cudaStream_t st) {
-  c->k.pack = nullptr;
-  if (!c->pack_buf || getenv("MIMGPU_FORCE_GENERIC") != nullptr) return MIMGPU_OK;
-  if (small_pack_launch_x(c->k, c->pack_buf, 0, c->sh.B, st) != 0) return MIMGPU_OK;
+  if (small_pack_launch_x(c->k, c->pack_buf, 0, c->sh.B, st) != 0) return fail(MIMGPU_ERR_CUDA, "k_pack_knots launch failed");
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(MIMGPU_ERR_CUDA, std::string("k_pack_knots: ") + cudaGetErrorString(e));
   c->launches++;
   c->k.pack = c->pack_buf;
+  c->pack_dirty = false;
   return MIMGPU_OK;
+}
+
+static int ensure_in_buf(mimgpu_ctx* c, size_t n[20]) {
+  const size_t tot = deriv_sizes(c->sh, n);
+  if (!c->in_buf) {
+    CU(cudaMalloc(&c->in_buf, tot * sizeof(double)));
+    c->in_doubles = tot;
+  }
+  return MIMGPU_OK;
+}
+
+/* Records mode: rebuild the field-major arrays (into the ctx's own buffer) for the paths the record
+ * kernel does not serve.  Caller-owned records are re-read every time (they may have changed). */
+static int ensure_fields(mimgpu_ctx* c, cudaStream_t st) {
+  if (!c->records_mode || (c->fields_valid && !c->attached)) return MIMGPU_OK;
+  size_t n[20];
+  int rc = ensure_in_buf(c, n);
+  if (rc) return rc;
+  const double** slot[20];
+  deriv_slots(c->k, slot);
+  double* q = c->in_buf;
+  for (int i = 0; i < 19; ++i) { /* slot 19 (cost) keeps the pointer given with the records */
+    *slot[i] = n[i] ? q : nullptr;
+    q += (n[i] + 1) & ~(size_t)1;
+  }
+  if (small_unpack_inputs_launch_x(c->k, c->k.pack, st) != 0) return fail(MIMGPU_ERR_CUDA, "k_unpack_records launch failed");
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(MIMGPU_ERR_CUDA, std::string("k_unpack_records: ") + cudaGetErrorString(e));
+  c->launches++;
+  c->fields_valid = true;
+  return MIMGPU_OK;
+}
+
+static void inputs_changed(mimgpu_ctx* c) {
+  c->have_inputs = true;
+  c->extras_stale = false; /* lazily materialised members of an earlier direction belong to the old inputs */
+  c->spill_packed = false;
 }
 
 int mimgpu_upload(mimgpu_ctx* c, const mimgpu_derivs* d, int memkind, void* stream) {
@@ -336,35 +394,81 @@ int mimgpu_upload(mimgpu_ctx* c, const mimgpu_derivs* d, int memkind, void* stre
   cudaStream_t st = (cudaStream_t)stream;
   CU(cudaSetDevice(c->device));
   size_t n[20];
-  const size_t tot = deriv_sizes(c->sh, n);
+  deriv_sizes(c->sh, n);
   const double* src[20] = {d->Fx, d->Fu, d->Lxx, d->Lxu, d->Luu, d->Lx, d->Lu, d->fs, d->LxxT, d->LxT,
                            d->Gx, d->Gu, d->g, d->g_lb, d->g_ub, d->GxT, d->gT, d->g_lbT, d->g_ubT, d->cost};
   for (int i = 0; i < 19; ++i)
     if (n[i] && !src[i]) return fail(MIMGPU_ERR_INVALID, "missing derivative array #" + std::to_string(i));
   const double** slot[20];
   deriv_slots(c->k, slot);
+  c->last_stream = st;
   if (memkind == MIMGPU_MEM_DEVICE) {
     for (int i = 0; i < 20; ++i) *slot[i] = n[i] ? src[i] : nullptr;
-    c->have_inputs = true;
-    return pack_inputs(c, st);
-  }
-  if (memkind != MIMGPU_MEM_HOST) return fail(MIMGPU_ERR_INVALID, "bad memkind");
-  if (!c->in_buf) {
-    CU(cudaMalloc(&c->in_buf, tot * sizeof(double)));
-    c->in_doubles = tot;
-  }
-  double* p = c->in_buf;
-  for (int i = 0; i < 20; ++i) {
-    if (n[i] && src[i]) {
-      CU(cudaMemcpyAsync(p, src[i], n[i] * sizeof(double), cudaMemcpyHostToDevice, st));
-      *slot[i] = p;
-    } else {
-      *slot[i] = nullptr;
+    c->attached = true;
+  } else if (memkind == MIMGPU_MEM_HOST) {
+    int rc = ensure_in_buf(c, n);
+    if (rc) return rc;
+    double* p = c->in_buf;
+    for (int i = 0; i < 20; ++i) {
+      if (n[i] && src[i]) {
+        CU(cudaMemcpyAsync(p, src[i], n[i] * sizeof(double), cudaMemcpyHostToDevice, st));
+        *slot[i] = p;
+      } else {
+        *slot[i] = nullptr;
+      }
+      p += (n[i] + 1) & ~(size_t)1;
     }
-    p += (n[i] + 1) & ~(size_t)1;
+    c->attached = false;
+  } else {
+    return fail(MIMGPU_ERR_INVALID, "bad memkind");
   }
-  c->have_inputs = true;
-  return pack_inputs(c, st);
+  c->records_mode = false;
+  c->fields_valid = true;
+  c->k.pack = nullptr;
+  c->pack_dirty = true;
+  inputs_changed(c);
+  return MIMGPU_OK;
+}
+
+int mimgpu_get_record_layout(const mimgpu_ctx* c, mimgpu_record_layout* out) {
+  if (!c || !out) return fail(MIMGPU_ERR_INVALID, "null pointer");
+  int v[16];
+  if (!(c->use_small & 2) || small_record_offsets_x(c->sh, v) != 0)
+    return fail(MIMGPU_ERR_UNSUPPORTED, "shape has no knot-record kernel");
+  out->rec_doubles = v[0]; out->term_doubles = v[1]; out->problem_doubles = v[2];
+  out->off_fs = v[3]; out->off_Lxx = v[4]; out->off_Lxu = v[5]; out->off_Luu = v[6]; out->off_Lx = v[7];
+  out->off_Lu = v[8]; out->off_Fx = v[9]; out->off_Fu = v[10];
+  out->toff_fs = v[11]; out->toff_Lxx = v[12]; out->toff_Lx = v[13];
+  out->reserved[0] = out->reserved[1] = 0;
+  return MIMGPU_OK;
+}
+
+int mimgpu_upload_records(mimgpu_ctx* c, const double* records, const double* cost, int memkind, void* stream) {
+  if (!c || !records) return fail(MIMGPU_ERR_INVALID, "null pointer");
+  if (!(c->use_small & 2) || !c->pack_buf) return fail(MIMGPU_ERR_UNSUPPORTED, "shape has no knot-record kernel");
+  if (c->sh.ng || c->sh.ngT) return fail(MIMGPU_ERR_UNSUPPORTED, "knot records carry no constraint blocks (ng = ngT = 0 only)");
+  cudaStream_t st = (cudaStream_t)stream;
+  CU(cudaSetDevice(c->device));
+  c->last_stream = st;
+  if (memkind == MIMGPU_MEM_DEVICE) {
+    if ((uintptr_t)records & 15) return fail(MIMGPU_ERR_INVALID, "records must be 16-byte aligned");
+    c->k.pack = records;
+    c->k.cost = cost;
+    c->attached = true;
+  } else if (memkind == MIMGPU_MEM_HOST) {
+    CU(cudaMemcpyAsync(c->pack_buf, records, c->pack_pp * (size_t)c->sh.B * sizeof(double), cudaMemcpyHostToDevice, st));
+    if (cost) CU(cudaMemcpyAsync(c->cost_buf, cost, (size_t)c->sh.B * sizeof(double), cudaMemcpyHostToDevice, st));
+    c->k.pack = c->pack_buf;
+    c->k.cost = cost ? c->cost_buf : nullptr;
+    c->attached = false;
+  } else {
+    return fail(MIMGPU_ERR_INVALID, "bad memkind");
+  }
+  c->records_mode = true;
+  c->fields_valid = false;
+  c->pack_dirty = false;
+  inputs_changed(c);
+  return MIMGPU_OK;
 }
 
 int mimgpu_set_reg(mimgpu_ctx* c, const double* preg, const double* dreg, void* stream) {
@@ -413,6 +517,10 @@ int mimgpu_set_field(mimgpu_ctx* c, int field, const double* src, void* stream) 
   if (c->field_n[field])
     CU(cudaMemcpyAsync(c->field[field], src, c->field_n[field] * sizeof(double), cudaMemcpyHostToDevice,
                        (cudaStream_t)stream));
+  /* a member written by the caller is no longer "to be materialised from the last fast SQP launch" */
+  if (field == MIMGPU_F_VXX || field == MIMGPU_F_VX || field == MIMGPU_F_K || field == MIMGPU_F_KFF) c->spill_packed = false;
+  if (field == MIMGPU_F_QU || field == MIMGPU_F_QUUK || field == MIMGPU_F_QUU_LLT) c->extras_stale = false;
+  c->last_stream = (cudaStream_t)stream;
   return MIMGPU_OK;
 }
 
@@ -423,6 +531,14 @@ static int pre_launch(mimgpu_ctx* c) {
   cudaError_t e = cudaSetDevice(c->device);
   if (e != cudaSuccess) return fail(MIMGPU_ERR_CUDA, cudaGetErrorString(e));
   return MIMGPU_OK;
+}
+/* Shapes outside the template lists run the shape-generic CTA kernels (correct, but far from the
+ * specialised ones): say so once per ctx instead of silently. */
+static void warn_generic(mimgpu_ctx* c, const char* what) {
+  if (c->warned_generic || c->force_generic) return;
+  c->warned_generic = true;
+  fprintf(stderr, "mimgpu: %s direction for shape (nx=%d, nu=%d, ng=%d) has no specialised kernel: running the "
+                  "shape-generic CTA kernel\n", what, c->sh.nx, c->sh.nu, c->sh.ng);
 }
 static int post_launch(mimgpu_ctx* c, const char* what) {
   cudaError_t e = cudaGetLastError();
@@ -438,8 +554,21 @@ int mimgpu_sqp_direction(mimgpu_ctx* c, const mimgpu_sqp_params* p, void* stream
   if (c->k.n_active == 0) return MIMGPU_OK;
   SqpKPar kp{p->preg, p->dreg, p->mu_dynamic, p->is_feasible};
   cudaStream_t st = (cudaStream_t)stream;
-  if (c->use_small && getenv("MIMGPU_FORCE_GENERIC") == nullptr) {
-    rc = small_sqp_direction_launch_x(c->k, kp, 0, st);
+  c->last_stream = st;
+  c->last_kind = 1;
+  const bool fast = (c->use_small & 2) && c->pack_buf && !c->force_generic && !c->small_alt;
+  if (fast && !c->records_mode && (c->pack_dirty || c->attached)) {
+    /* field-major inputs: (re)build the knot records.  Caller-owned device inputs are re-read at every
+     * call -- every computeDirection follows a fresh calcDiff (src/sqp.cpp:224-228) */
+    rc = pack_inputs(c, st);
+    if (rc) return rc;
+  }
+  if (!fast) {
+    rc = ensure_fields(c, st);
+    if (rc) return rc;
+  }
+  if (c->use_small && !c->force_generic) {
+    rc = small_sqp_direction_launch_x(c->k, kp, fast ? 0 : 1, st);
     if (rc >= 0) {
       c->extras_stale = (rc == 0);
       c->spill_packed = (rc == 0);
@@ -449,30 +578,29 @@ int mimgpu_sqp_direction(mimgpu_ctx* c, const mimgpu_sqp_params* p, void* stream
   }
   c->extras_stale = false;
   c->spill_packed = false;
-  if (c->cplan.ok && !c->use_small && getenv("MIMGPU_FORCE_GENERIC") == nullptr &&
+  if (c->cplan.ok && !c->use_small && !c->force_generic &&
       (((uintptr_t)c->k.Fx | (uintptr_t)c->k.Fu) & 15) == 0 && cta_sqp_launch_x(c->k, kp, false, c->cplan, st) == 0)
     return post_launch(c, "k_sqp_direction_cta");
+  warn_generic(c, "SQP");
   k_sqp_direction_generic<<<c->k.n_active, c->nt, c->smem_bytes, st>>>(c->k, kp);
   return post_launch(c, "k_sqp_direction_generic");
 }
 
-/* SolverSQP::computeDirection for HOST-resident derivatives, end to end: the batch is cut into
- * `n_chunks` slices; slice i is uploaded, repacked, solved and its dx_ / du_ / lag_mul_ / KKT_
+/* SolverSQP::computeDirection for HOST-resident inputs, end to end: the batch is cut into
+ * `n_chunks` slices; slice i is uploaded, (re-laid-out,) solved and its dx_ / du_ / lag_mul_ / KKT_
  * downloaded on one of two internal streams, so the PCIe copies of both directions overlap each
- * other and the kernels of the neighbouring slices.  Same results as mimgpu_upload +
- * mimgpu_sqp_direction + mimgpu_download; returns after everything has landed in the host
- * arrays (pin them).  Falls back to that sequence when the shape has no sliceable kernel. */
-int mimgpu_sqp_direction_host(mimgpu_ctx* c, const mimgpu_derivs* d, const mimgpu_sqp_params* p, double* dx,
-                              double* du, double* lag_mul, double* kkt, int32_t n_chunks) {
-  if (!c || !d || !p) return fail(MIMGPU_ERR_INVALID, "null pointer");
+ * other and the kernels of the neighbouring slices.  Inputs are either the field-major arrays (d) or
+ * knot records (records, cost).  Returns after everything has landed in the host arrays. */
+static int sqp_direction_host_impl(mimgpu_ctx* c, const mimgpu_derivs* d, const double* records, const double* cost,
+                                   const mimgpu_sqp_params* p, double* dx, double* du, double* lag_mul, double* kkt,
+                                   int32_t n_chunks) {
   CU(cudaSetDevice(c->device));
   const mimgpu_shape& sh = c->sh;
   const size_t B = sh.B, T = sh.T, nx = sh.nx, nu = sh.nu;
-  const bool sliceable = c->pack_buf && (c->use_small & 2) && getenv("MIMGPU_FORCE_GENERIC") == nullptr &&
-                         getenv("MIMGPU_SMALL_FULL") == nullptr && getenv("MIMGPU_SMALL_NOMMA") == nullptr &&
-                         !c->k.active;
+  const bool sliceable = c->pack_buf && (c->use_small & 2) && !c->force_generic && !c->small_alt && !c->k.active;
   if (!sliceable || n_chunks <= 1) {
-    int rc = mimgpu_upload(c, d, MIMGPU_MEM_HOST, nullptr);
+    int rc = records ? mimgpu_upload_records(c, records, cost, MIMGPU_MEM_HOST, nullptr)
+                     : mimgpu_upload(c, d, MIMGPU_MEM_HOST, nullptr);
     if (rc == MIMGPU_OK) rc = mimgpu_sqp_direction(c, p, nullptr);
     if (rc == MIMGPU_OK && dx) rc = mimgpu_download(c, MIMGPU_F_DX, dx, nullptr);
     if (rc == MIMGPU_OK && du) rc = mimgpu_download(c, MIMGPU_F_DU, du, nullptr);
@@ -485,27 +613,30 @@ int mimgpu_sqp_direction_host(mimgpu_ctx* c, const mimgpu_derivs* d, const mimgp
   for (int i = 0; i < 2; ++i)
     if (!c->pipe_st[i]) CU(cudaStreamCreateWithFlags(&c->pipe_st[i], cudaStreamNonBlocking));
   size_t n[20];
-  const size_t tot = deriv_sizes(sh, n);
-  const double* src[20] = {d->Fx, d->Fu, d->Lxx, d->Lxu, d->Luu, d->Lx, d->Lu, d->fs, d->LxxT, d->LxT,
-                           d->Gx, d->Gu, d->g, d->g_lb, d->g_ub, d->GxT, d->gT, d->g_lbT, d->g_ubT, d->cost};
-  for (int i = 0; i < 19; ++i)
-    if (n[i] && !src[i]) return fail(MIMGPU_ERR_INVALID, "missing derivative array #" + std::to_string(i));
-  if (!c->in_buf) {
-    CU(cudaMalloc(&c->in_buf, tot * sizeof(double)));
-    c->in_doubles = tot;
-  }
+  const double* src[20] = {};
+  double* dst[20] = {};
   const double** slot[20];
   deriv_slots(c->k, slot);
-  double* dst[20];
-  {
+  if (!records) {
+    int rc = ensure_in_buf(c, n);
+    if (rc) return rc;
+    const double* s2[20] = {d->Fx, d->Fu, d->Lxx, d->Lxu, d->Luu, d->Lx, d->Lu, d->fs, d->LxxT, d->LxT,
+                            d->Gx, d->Gu, d->g, d->g_lb, d->g_ub, d->GxT, d->gT, d->g_lbT, d->g_ubT, d->cost};
+    for (int i = 0; i < 20; ++i) src[i] = s2[i];
+    for (int i = 0; i < 19; ++i)
+      if (n[i] && !src[i]) return fail(MIMGPU_ERR_INVALID, "missing derivative array #" + std::to_string(i));
     double* q = c->in_buf;
     for (int i = 0; i < 20; ++i) {
       dst[i] = q;
       *slot[i] = (n[i] && src[i]) ? q : nullptr;
       q += (n[i] + 1) & ~(size_t)1;
     }
+  } else {
+    if (sh.ng || sh.ngT) return fail(MIMGPU_ERR_UNSUPPORTED, "knot records carry no constraint blocks");
+    c->k.cost = cost ? c->cost_buf : nullptr;
   }
-  CU(cudaDeviceSynchronize()); /* earlier work of this ctx on other streams is done with the buffers */
+  /* earlier asynchronous work of this ctx (on the caller's stream) is done with the buffers */
+  if (c->last_stream != c->pipe_st[0] && c->last_stream != c->pipe_st[1]) CU(cudaStreamSynchronize(c->last_stream));
   SqpKPar kp{p->preg, p->dreg, p->mu_dynamic, p->is_feasible};
   KArgs ka = c->k;
   ka.pack = c->pack_buf;
@@ -513,14 +644,20 @@ int mimgpu_sqp_direction_host(mimgpu_ctx* c, const mimgpu_derivs* d, const mimgp
   for (size_t b0 = 0, ci = 0; b0 < B; b0 += per, ++ci) {
     const size_t nb = (b0 + per <= B) ? per : B - b0;
     cudaStream_t st = c->pipe_st[ci & 1];
-    for (int i = 0; i < 20; ++i) {
-      if (!(n[i] && src[i])) continue;
-      const size_t pb = n[i] / B; /* doubles per problem of this field */
-      CU(cudaMemcpyAsync(dst[i] + b0 * pb, src[i] + b0 * pb, nb * pb * sizeof(double), cudaMemcpyHostToDevice, st));
+    if (records) {
+      CU(cudaMemcpyAsync(c->pack_buf + b0 * c->pack_pp, records + b0 * c->pack_pp, nb * c->pack_pp * sizeof(double),
+                         cudaMemcpyHostToDevice, st));
+      if (cost) CU(cudaMemcpyAsync(c->cost_buf + b0, cost + b0, nb * sizeof(double), cudaMemcpyHostToDevice, st));
+    } else {
+      for (int i = 0; i < 20; ++i) {
+        if (!(n[i] && src[i])) continue;
+        const size_t pb = n[i] / B; /* doubles per problem of this field */
+        CU(cudaMemcpyAsync(dst[i] + b0 * pb, src[i] + b0 * pb, nb * pb * sizeof(double), cudaMemcpyHostToDevice, st));
+      }
+      if (small_pack_launch_x(ka, c->pack_buf, (int)b0, (int)nb, st) != 0)
+        return fail(MIMGPU_ERR_CUDA, "k_pack_knots launch failed");
+      c->launches++;
     }
-    if (small_pack_launch_x(ka, c->pack_buf, (int)b0, (int)nb, st) != 0)
-      return fail(MIMGPU_ERR_CUDA, "k_pack_knots launch failed");
-    c->launches++;
     ka.first = (int32_t)b0;
     ka.n_active = (int32_t)nb;
     if (small_sqp_direction_launch_x(ka, kp, 0, st) != 0) return fail(MIMGPU_ERR_CUDA, "k_sqp_direction_small_gj launch failed");
@@ -538,11 +675,31 @@ int mimgpu_sqp_direction_host(mimgpu_ctx* c, const mimgpu_derivs* d, const mimgp
   CU(cudaStreamSynchronize(c->pipe_st[0]));
   CU(cudaStreamSynchronize(c->pipe_st[1]));
   c->k.pack = c->pack_buf;
-  c->have_inputs = true;
+  c->attached = false;
+  c->records_mode = records != nullptr;
+  c->fields_valid = !c->records_mode;
+  c->pack_dirty = false;
+  inputs_changed(c);
   c->extras_stale = true;
   c->spill_packed = true;
   c->last_sqp = kp;
+  c->last_kind = 1;
+  c->last_stream = c->pipe_st[0];
   return MIMGPU_OK;
+}
+
+int mimgpu_sqp_direction_host(mimgpu_ctx* c, const mimgpu_derivs* d, const mimgpu_sqp_params* p, double* dx,
+                              double* du, double* lag_mul, double* kkt, int32_t n_chunks) {
+  if (!c || !d || !p) return fail(MIMGPU_ERR_INVALID, "null pointer");
+  return sqp_direction_host_impl(c, d, nullptr, nullptr, p, dx, du, lag_mul, kkt, n_chunks);
+}
+
+int mimgpu_sqp_direction_host_records(mimgpu_ctx* c, const double* records, const double* cost,
+                                      const mimgpu_sqp_params* p, double* dx, double* du, double* lag_mul,
+                                      double* kkt, int32_t n_chunks) {
+  if (!c || !records || !p) return fail(MIMGPU_ERR_INVALID, "null pointer");
+  if (!(c->use_small & 2) || !c->pack_buf) return fail(MIMGPU_ERR_UNSUPPORTED, "shape has no knot-record kernel");
+  return sqp_direction_host_impl(c, nullptr, records, cost, p, dx, du, lag_mul, kkt, n_chunks);
 }
 
 int mimgpu_fddp_direction(mimgpu_ctx* c, const mimgpu_sqp_params* p, void* stream) {
@@ -553,10 +710,15 @@ int mimgpu_fddp_direction(mimgpu_ctx* c, const mimgpu_sqp_params* p, void* strea
   SqpKPar kp{p->preg, p->dreg, p->mu_dynamic, p->is_feasible};
   c->extras_stale = false;
   c->spill_packed = false;
-  if (c->cplan.ok && getenv("MIMGPU_FORCE_GENERIC") == nullptr &&
+  c->last_stream = (cudaStream_t)stream;
+  c->last_kind = 2;
+  rc = ensure_fields(c, (cudaStream_t)stream);
+  if (rc) return rc;
+  if (c->cplan.ok && !c->force_generic &&
       (((uintptr_t)c->k.Fx | (uintptr_t)c->k.Fu) & 15) == 0 &&
       cta_sqp_launch_x(c->k, kp, true, c->cplan, (cudaStream_t)stream) == 0)
     return post_launch(c, "k_fddp_direction_cta");
+  if (!c->use_small) warn_generic(c, "FDDP");
   k_fddp_direction_generic<<<c->k.n_active, c->nt, c->smem_bytes, (cudaStream_t)stream>>>(c->k, kp);
   return post_launch(c, "k_fddp_direction_generic");
 }
@@ -565,6 +727,9 @@ int mimgpu_csqp_calc_norms(mimgpu_ctx* c, void* stream) {
   int rc = pre_launch(c);
   if (rc) return rc;
   if (c->k.n_active == 0) return MIMGPU_OK;
+  c->last_stream = (cudaStream_t)stream;
+  rc = ensure_fields(c, (cudaStream_t)stream);
+  if (rc) return rc;
   k_csqp_calc_norms<<<c->k.n_active, 128, 0, (cudaStream_t)stream>>>(c->k);
   return post_launch(c, "k_csqp_calc_norms");
 }
@@ -574,6 +739,7 @@ int mimgpu_csqp_reset_rho(mimgpu_ctx* c, const mimgpu_csqp_params* p, void* stre
   if (rc) return rc;
   if (!p) return fail(MIMGPU_ERR_INVALID, "null params");
   if (c->k.n_active == 0) return MIMGPU_OK;
+  c->last_stream = (cudaStream_t)stream;
   k_csqp_reset_rho<<<c->k.n_active, 128, 0, (cudaStream_t)stream>>>(c->k, p->rho_sparse_base, p->rho_min);
   return post_launch(c, "k_csqp_reset_rho");
 }
@@ -587,13 +753,30 @@ int mimgpu_csqp_direction(mimgpu_ctx* c, const mimgpu_csqp_params* p, int with_k
   CsqpKPar kp;
   kp.q = *p;
   kp.with_kkt = with_kkt;
-  if (c->splan.ok && getenv("MIMGPU_FORCE_GENERIC") == nullptr) {
-    /* TMA bulk copies need 16-byte aligned sources (block sizes are even by construction) */
-    const uintptr_t al = (uintptr_t)c->k.Fx | (uintptr_t)c->k.Fu | (uintptr_t)c->k.Gx | (uintptr_t)c->k.Gu;
-    if ((al & 15) == 0 && stream_csqp_launch_x(c->k, *p, with_kkt, c->splan, (cudaStream_t)stream) == 0)
-      return post_launch(c, "k_csqp_direction_stream");
+  cudaStream_t st = (cudaStream_t)stream;
+  c->last_kind = 3;
+  c->last_stream = st;
+  rc = ensure_fields(c, st);
+  if (rc) return rc;
+  /* the fast SQP kernel's lazily materialised members are overwritten by this call */
+  c->extras_stale = false;
+  c->spill_packed = false;
+  /* 16-byte rows / TMA bulk copies need 16-byte aligned sources (block sizes are even by construction) */
+  const uintptr_t al = (uintptr_t)c->k.Fx | (uintptr_t)c->k.Fu | (uintptr_t)c->k.Gx | (uintptr_t)c->k.Gu;
+  if (c->aplan.ok && !c->force_generic && !c->csqp_stream && (al & 15) == 0) {
+    if (!c->admm_scr[0]) {
+      const size_t BT = (size_t)c->sh.B * c->sh.T, nx = c->sh.nx;
+      const size_t bytes[4] = {BT * nx * nx * 8, BT * nx * nx * 8, BT * nx * 8, BT * nx * 8};
+      for (int i = 0; i < 4; ++i) CU(cudaMalloc(&c->admm_scr[i], bytes[i]));
+    }
+    if (admm_csqp_launch_x(c->k, *p, with_kkt, c->aplan, c->admm_scr, st) == 0)
+      return post_launch(c, "k_csqp_direction_admm");
   }
-  k_csqp_direction_generic<<<c->k.n_active, c->nt, c->smem_bytes, (cudaStream_t)stream>>>(c->k, kp);
+  if (c->splan.ok && !c->force_generic && (al & 15) == 0 &&
+      stream_csqp_launch_x(c->k, *p, with_kkt, c->splan, st) == 0)
+    return post_launch(c, "k_csqp_direction_stream");
+  warn_generic(c, "CSQP");
+  k_csqp_direction_generic<<<c->k.n_active, c->nt, c->smem_bytes, st>>>(c->k, kp);
   return post_launch(c, "k_csqp_direction_generic");
 }
 
@@ -614,6 +797,8 @@ static int refresh_extras(mimgpu_ctx* c, int field, cudaStream_t st) {
   }
   if (!c->extras_stale) return MIMGPU_OK;
   if (field != MIMGPU_F_QU && field != MIMGPU_F_QUUK && field != MIMGPU_F_QUU_LLT) return MIMGPU_OK;
+  int rc0 = ensure_fields(c, st);
+  if (rc0) return rc0;
   if (c->k.n_active > 0) {
     if (small_sqp_direction_launch_x(c->k, c->last_sqp, 1, st) != 1)
       return fail(MIMGPU_ERR_CUDA, "full-spill kernel launch failed");
@@ -637,14 +822,13 @@ int mimgpu_download(mimgpu_ctx* c, int field, double* dst, void* stream) {
   return MIMGPU_OK;
 }
 
-int mimgpu_field_ptr(mimgpu_ctx* c, int field, double** dev_ptr, int64_t* n_doubles) {
+int mimgpu_field_ptr(mimgpu_ctx* c, int field, double** dev_ptr, int64_t* n_doubles, void* stream) {
   if (!c) return fail(MIMGPU_ERR_INVALID, "null pointer");
   if (field < 0 || field >= MIMGPU_F_COUNT) return fail(MIMGPU_ERR_INVALID, "bad field id");
-  if (c->extras_stale || c->spill_packed) {
+  if (c->extras_stale || c->spill_packed) { /* lazily materialised members: enqueued on the caller's stream */
     CU(cudaSetDevice(c->device));
-    int rc = refresh_extras(c, field, (cudaStream_t)0);
+    int rc = refresh_extras(c, field, (cudaStream_t)stream);
     if (rc) return rc;
-    CU(cudaStreamSynchronize((cudaStream_t)0));
   }
   if (dev_ptr) *dev_ptr = c->field[field];
   if (n_doubles) *n_doubles = (int64_t)c->field_n[field];
@@ -683,12 +867,9 @@ int mimgpu_summary_reduce(mimgpu_ctx* c, double termination_tol, mimgpu_summary*
   if (!c || !out) return fail(MIMGPU_ERR_INVALID, "null pointer");
   CU(cudaSetDevice(c->device));
   cudaStream_t st = (cudaStream_t)stream;
-  /* csqp = 1 when any ADMM call has set qp_iters (> 0); decided on the device data */
-  int32_t first_it = 0;
-  CU(cudaMemcpyAsync(&first_it, c->k.qp_iters, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
-  CU(cudaStreamSynchronize(st));
+  const int csqp_kind = (c->last_kind == 3); /* n_converged counts ADMM breaks for CSQP, KKT <= tol otherwise */
   k_summary<<<1, 1024, 0, st>>>(c->k.scal + (size_t)MIMGPU_S_KKT * c->sh.B, c->k.qp_iters, c->k.status,
-                                c->k.converged, c->sh.B, termination_tol, first_it > 0, (SummaryDev*)c->summary_dev);
+                                c->k.converged, c->sh.B, termination_tol, csqp_kind, (SummaryDev*)c->summary_dev);
   int rc = post_launch(c, "k_summary");
   if (rc) return rc;
   SummaryDev h;

@@ -16,4 +16,8 @@ int small_pack_launch_x(const KArgs& a, double* pack, int b0, int nb, cudaStream
   return small_pack_launch(a, pack, b0, nb, st);
 }
 int small_unpack_launch_x(const KArgs& a, cudaStream_t st) { return small_unpack_launch(a, st); }
+int small_unpack_inputs_launch_x(const KArgs& a, const double* pack, cudaStream_t st) {
+  return small_unpack_inputs_launch(a, pack, st);
+}
+int small_record_offsets_x(const mimgpu_shape& s, int out[16]) { return small_record_offsets(s, out); }
 }  // namespace mimgpu

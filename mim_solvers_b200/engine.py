@@ -69,6 +69,56 @@ class BatchEngine:
         self._keep = tensors
         check(self._lib.mimgpu_upload(self._ctx, C.byref(d), _capi.MEM_DEVICE, self.stream), "mimgpu_upload")
 
+    # ---- knot-record inputs (mimgpu_upload_records) -------------------------------
+    def record_layout(self) -> _capi.RecordLayout:
+        """Block offsets of the knot-record layout; raises MimGpuError for shapes without it."""
+        L = _capi.RecordLayout()
+        check(self._lib.mimgpu_get_record_layout(self._ctx, C.byref(L)), "mimgpu_get_record_layout")
+        return L
+
+    def pack_records(self, batch: OCPBatch, out: np.ndarray | None = None) -> np.ndarray:
+        """What a producer-side packer does: every block of every knot copied to its place in the
+        record layout (host side, numpy).  Returns a [B, problem_doubles] float64 array."""
+        L = self.record_layout()
+        B, T, nx, nu = batch.B, batch.T, batch.nx, batch.nu
+        rec = np.empty((B, L.problem_doubles)) if out is None else out
+        run = rec[:, :T * L.rec_doubles].reshape(B, T, L.rec_doubles)
+        term = rec[:, T * L.rec_doubles:]
+        A = batch.arrays
+        for name, off, n in (("Lxx", L.off_Lxx, nx * nx), ("Lxu", L.off_Lxu, nx * nu), ("Luu", L.off_Luu, nu * nu),
+                             ("Lx", L.off_Lx, nx), ("Lu", L.off_Lu, nu), ("Fx", L.off_Fx, nx * nx),
+                             ("Fu", L.off_Fu, nx * nu)):
+            run[:, :, off:off + n] = A[name].reshape(B, T, n)
+        run[:, :, L.off_fs:L.off_fs + nx] = A["fs"][:, :T]
+        term[:, L.toff_fs:L.toff_fs + nx] = A["fs"][:, T]
+        term[:, L.toff_Lxx:L.toff_Lxx + nx * nx] = A["LxxT"].reshape(B, nx * nx)
+        term[:, L.toff_Lx:L.toff_Lx + nx] = A["LxT"]
+        return rec
+
+    def upload_records(self, records: np.ndarray, cost: np.ndarray | None = None):
+        """Host knot records -> device (one async H2D copy)."""
+        assert records.dtype == np.float64 and records.flags["C_CONTIGUOUS"]
+        self._keep = (records, cost)
+        check(self._lib.mimgpu_upload_records(self._ctx, records.ctypes.data, _capi.as_ptr(cost), _capi.MEM_HOST,
+                                              self.stream), "mimgpu_upload_records")
+
+    def attach_records(self, records, cost=None):
+        """Device-resident knot records (torch CUDA float64 tensors): zero-copy, no re-layout pass."""
+        assert records.is_cuda and records.is_contiguous() and str(records.dtype) == "torch.float64"
+        self._keep = (records, cost)
+        check(self._lib.mimgpu_upload_records(self._ctx, records.data_ptr(), None if cost is None else cost.data_ptr(),
+                                              _capi.MEM_DEVICE, self.stream), "mimgpu_upload_records")
+
+    def sqp_direction_host_records(self, records: np.ndarray, cost=None, params=None, *, dx=None, du=None,
+                                   lag_mul=None, kkt=None, n_chunks: int = 8):
+        """mimgpu_sqp_direction_host_records: host records in, dx/du/lag_mul/KKT out, overlapped slices."""
+        p = params or _capi.default_sqp_params()
+        self._keep = (records, cost)
+        ptr = lambda a: None if a is None else a.ctypes.data
+        check(self._lib.mimgpu_sqp_direction_host_records(self._ctx, records.ctypes.data, ptr(cost), C.byref(p), ptr(dx),
+                                                          ptr(du), ptr(lag_mul), ptr(kkt), int(n_chunks)),
+              "mimgpu_sqp_direction_host_records")
+
     def set_reg(self, preg=None, dreg=None):
         p = None if preg is None else np.ascontiguousarray(preg, dtype=np.float64)
         d = None if dreg is None else np.ascontiguousarray(dreg, dtype=np.float64)

@@ -194,3 +194,103 @@ def test_gpu_sqp_direction_host_matches_stepwise(eng, n_chunks):
     assert np.array_equal(kkt, a.scalar("KKT"))
     for n in ("K", "Vxx", "Quu_llt"):
         assert np.array_equal(b.field(n), a.field(n)), n
+
+
+def test_gpu_knot_records_layout(eng, oracle_lib):
+    """Second input layout of the ABI (mimgpu_upload_records): the producer writes knot records, no
+    k_pack_knots pass.  Host records, device-attached records (zero copy, re-read at every call) and
+    the chunked host path are bit-identical to the field-major path; entry points the record kernel
+    does not serve rebuild the field-major arrays on the device."""
+    import torch
+    from mim_solvers_b200.problems import make_random_batch
+    batch = make_random_batch(37, 20, 12, 6)
+    a = eng(batch)
+    a.sqp_direction()
+    ref = {n: a.field(n) for n in ("dx", "du", "lag_mul", "K", "Vxx", "Qu", "Quu_llt")}
+    kkt = a.scalar("KKT")
+    b = eng(shape=batch.shape())
+    L = b.record_layout()
+    assert L.problem_doubles == batch.T * L.rec_doubles + L.term_doubles
+    rec = b.pack_records(batch)
+    cost = np.ascontiguousarray(batch.arrays["cost"])
+    l0 = b.launch_count
+    b.upload_records(rec, cost)
+    b.sqp_direction()
+    assert b.launch_count - l0 == 1, "records path must not launch a re-layout kernel"
+    for n in ("dx", "du", "lag_mul", "K", "Vxx"):
+        assert np.array_equal(b.field(n), ref[n]), n
+    assert np.array_equal(b.scalar("KKT"), kkt) and np.array_equal(b.scalar("merit"), a.scalar("merit"))
+    for n in ("Qu", "Quu_llt"):   # full-spill recomputation needs the field-major arrays: rebuilt on demand
+        assert np.array_equal(b.field(n), ref[n]), n
+    # device-attached records, mutated in place between two calls
+    c = eng(shape=batch.shape())
+    drec = torch.from_numpy(rec).cuda()
+    c.attach_records(drec, torch.from_numpy(cost).cuda())
+    c.sqp_direction()
+    assert np.array_equal(c.field("dx"), ref["dx"])
+    batch2 = make_random_batch(37, 20, 12, 6, first=1000)
+    drec.copy_(torch.from_numpy(c.pack_records(batch2)))
+    c.sqp_direction()
+    o = oracle_lib.Oracle(batch2); o.sqp_direction()
+    from helpers import assert_close
+    for n in ("dx", "du", "lag_mul"):
+        assert_close(c.field(n), o.field(n), 1e-9, n, per_problem=True)
+    assert_close(c.field("Qu"), o.field("Qu"), 1e-9, "Qu after in-place change", per_problem=True)
+    # chunked host path on records
+    d = eng(shape=batch.shape())
+    sh = batch.shape()
+    out = {n: np.empty(sh.field_shape(n)) for n in ("dx", "du", "lag_mul")}
+    k2 = np.empty(sh.B)
+    d.sqp_direction_host_records(rec, cost, None, dx=out["dx"], du=out["du"], lag_mul=out["lag_mul"], kkt=k2, n_chunks=5)
+    for n in out:
+        assert np.array_equal(out[n], ref[n]), n
+    assert np.array_equal(k2, kkt)
+    # FDDP on a records ctx (needs the field-major arrays)
+    d.fddp_direction()
+    o1 = oracle_lib.Oracle(batch); o1.fddp_direction()
+    assert_close(d.scalar("dg"), o1.scalar("dg"), 1e-9, "dg", per_problem=True)
+
+
+@pytest.mark.parametrize("B,T,nx,nu", [(9, 15, 12, 6), (4, 8, 36, 12)])
+def test_gpu_attached_inputs_are_reread(eng, oracle_lib, B, T, nx, nu):
+    """MIMGPU_MEM_DEVICE inputs are the caller's memory: updating them in place and calling the
+    direction again must use the NEW values (the small shapes re-layout them at every call)."""
+    import torch
+    from helpers import assert_close
+    from mim_solvers_b200.problems import make_random_batch
+    batch = make_random_batch(B, T, nx, nu)
+    g = eng(shape=batch.shape())
+    dev = {k: torch.from_numpy(v).cuda() for k, v in batch.arrays.items()}
+    g.attach_device(dev)
+    g.sqp_direction()
+    o = oracle_lib.Oracle(batch); o.sqp_direction()
+    assert_close(g.field("dx"), o.field("dx"), 1e-9, "dx", per_problem=True)
+    batch2 = make_random_batch(B, T, nx, nu, first=77)
+    for k, v in batch2.arrays.items():
+        dev[k].copy_(torch.from_numpy(v))
+    g.sqp_direction()
+    o2 = oracle_lib.Oracle(batch2); o2.sqp_direction()
+    for n in ("dx", "du", "lag_mul", "K", "Qu"):
+        assert_close(g.field(n), o2.field(n), 1e-9, n, per_problem=True)
+
+
+def test_gpu_member_flags_do_not_go_stale(eng, oracle_lib):
+    """After a fast SQP launch the members Vxx_ Vx_ K_ k_ live in spill records until asked for; a
+    CSQP direction on the same ctx, a new upload or mimgpu_set_field must drop that pending state."""
+    from helpers import assert_close
+    from mim_solvers_b200 import _capi
+    from mim_solvers_b200.problems import make_random_batch
+    batch = make_random_batch(5, 12, 12, 6)
+    g = eng(batch)
+    g.sqp_direction()
+    p = _capi.default_csqp_params(max_qp_iters=30)
+    g.csqp_calc_norms(); g.csqp_reset_rho(p); g.csqp_direction(p)
+    o = oracle_lib.Oracle(batch)
+    o.csqp_calc_norms(); o.csqp_reset_rho(p); o.csqp_direction(p)
+    for n in ("K", "k", "Vx", "Vxx", "Qu"):
+        assert_close(g.field(n), o.field(n), 1e-9, "after CSQP: " + n, per_problem=True)
+    s = g.summary(1e-6)
+    assert s["sum_qp_iters"] == int(np.asarray(o.qp_iters).sum())
+    g.sqp_direction()
+    g.set_field("K", np.zeros(batch.shape().field_shape("K")))
+    assert not g.field("K").any()
