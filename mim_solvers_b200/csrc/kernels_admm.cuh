@@ -48,18 +48,29 @@ namespace mimgpu {
 
 /* ------------------------------------------------------------------ shared memory */
 struct AdmmSmem {
-  int bars, red, uni, vb, ws0, wsn, total;
+  int bars, wbars, cbars, red, uni, vb, ws0, wsn, stg, total;
 };
+/* doubles of one warp's TMA stage in the knot-parallel phases: update = [K | Gx Gu (if stage_g)],
+ * gains = [Fu | LLT] */
 template <int NX, int NU>
-__host__ __device__ inline AdmmSmem admm_layout(int ng, int ngT, int nwarps, int ric_total) {
+__host__ __device__ inline int admm_stage_doubles(int ng, bool staged, bool stage_g) {
+  if (!staged) return 0;
+  const int a = NX * NU + (stage_g ? ng * (NX + NU) : 0), b = NX * NU + NU * NU;
+  return a > b ? a : b;
+}
+template <int NX, int NU>
+__host__ __device__ inline AdmmSmem admm_layout(int ng, int ngT, int nwarps, int ric_total, int stage_doubles) {
   AdmmSmem s;
   const int ngm = ng > ngT ? ng : ngT;
-  s.bars = 0;
-  s.red = 8;
-  s.uni = 8 + 64;
+  s.bars = 0;                         /* two mbarriers of the Riccati sweep */
+  s.wbars = 8;                        /* one mbarrier per warp (TMA stage of the knot-parallel phases) */
+  s.cbars = 8 + 16;                   /* up to eight mbarriers of the chains' TMA ring */
+  s.red = 8 + 16 + 8;
+  s.uni = 8 + 16 + 8 + 64;
   s.vb = s.uni;                       /* chain vector, double buffered */
-  s.ws0 = s.uni + 2 * NX;             /* per-warp scratch of the knot-parallel phases */
-  s.wsn = (2 * NX + 2 * NU + 3 * ngm + 1) & ~1;
+  s.ws0 = s.uni + 2 * NX;             /* per-warp scratch + stage of the knot-parallel phases */
+  s.stg = (2 * NX + 2 * NU + 3 * ngm + 1) & ~1;
+  s.wsn = s.stg + ((stage_doubles + 1) & ~1);
   const int a = 2 * NX + nwarps * s.wsn;
   s.total = s.uni + (a > ric_total ? a : ric_total);
   return s;
@@ -173,22 +184,24 @@ __device__ __forceinline__ double wsolve_llt(const double* L, double xi, int lan
   static_assert(NU <= 32, "one lane per control");
   const bool in = lane < NU;
   const int lc = in ? lane : 0;
+  /* 1 / L_jj once per knot (lane j), multiplied in: one division per lane instead of one per step */
+  const double rdiag = 1.0 / (in ? L[lc + NU * lc] : 1.0);
   double lv[NU];
 #pragma unroll
-  for (int j = 0; j < NU; ++j) lv[j] = (in && lane >= j) ? L[lc + NU * j] : 1.0;   /* column entries of my row */
+  for (int j = 0; j < NU; ++j) lv[j] = (in && lane > j) ? L[lc + NU * j] : 0.0;   /* column entries of my row */
 #pragma unroll
   for (int j = 0; j < NU; ++j) {
-    const double xj = __shfl_sync(MG_FULLMASK, xi / lv[j], j);
+    const double xj = __shfl_sync(MG_FULLMASK, xi * rdiag, j);
     if (lane == j) xi = xj;
-    else if (lane > j) xi = fma(-lv[j], xj, xi);
+    else xi = fma(-lv[j], xj, xi);   /* lv[j] = 0 for lanes <= j */
   }
 #pragma unroll
-  for (int j = 0; j < NU; ++j) lv[j] = (in && lane <= j) ? L[j + NU * lc] : 1.0;   /* row j, my column */
+  for (int j = 0; j < NU; ++j) lv[j] = (in && lane < j) ? L[j + NU * lc] : 0.0;   /* row j, my column */
 #pragma unroll
   for (int j = NU - 1; j >= 0; --j) {
-    const double xj = __shfl_sync(MG_FULLMASK, xi / lv[j], j);
+    const double xj = __shfl_sync(MG_FULLMASK, xi * rdiag, j);
     if (lane == j) xi = xj;
-    else if (lane < j) xi = fma(-lv[j], xj, xi);
+    else xi = fma(-lv[j], xj, xi);
   }
   return xi;
 }
@@ -200,6 +213,18 @@ __device__ __forceinline__ double warp_nmax_all(double v) {
 }
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+/* L2 prefetch: the knot-parallel phases and the chains pull the NEXT knots' blocks into L2 while the
+ * current ones are processed, so that the dependent steps of a knot pay L2 latency, not DRAM's. */
+__device__ __forceinline__ void pf_line(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+/* contiguous block, 16-byte aligned, even number of doubles: one bulk prefetch by one lane */
+__device__ __forceinline__ void pf_block(const double* p, int ndoubles, int lane) {
+  if (lane == 0 && ndoubles > 0) l2_prefetch(p, (uint32_t)ndoubles * 8u);
+}
+/* short vector: one 128-byte line per lane */
+__device__ __forceinline__ void pf_vec(const double* p, int ndoubles, int lane) {
+  if (lane >= 0 && lane * 16 < ndoubles) pf_line(p + lane * 16);
 }
 
 /* ----------------------------------------------------------- per-problem scratch */
@@ -264,6 +289,7 @@ static __device__ __noinline__ void admm_post_full(const Prob& p, const AdmmScr&
     });
     __syncwarp();
   }
+  fence_proxy_async(); /* Acl, b_t (and the sweep's K, LLT) were written through the generic proxy; TMA reads them */
 }
 
 /* --------------------------------------------------------------------- the chains */
@@ -271,70 +297,82 @@ static __device__ __noinline__ void admm_post_full(const Prob& p, const AdmmScr&
  * FWD: dx~_{t+1} = b_t + Acl_t dx~_t, t = 0 .. T-1
  * Four lanes per output row, the warps holding threads < nchain take part (named barrier 1), each
  * thread prefetches its slice of the next two knots' matrix through registers. */
+struct ChainSeq {
+  int slot;        /* ring slot of the next load */
+  uint32_t phase;  /* mbarrier phase parity of that slot */
+};
+template <int NX>
+__host__ __device__ constexpr int admm_chain_stage() { return NX * NX + 2 * NX; } /* [M | add0 | add1] */
+
 template <int NX, bool BWD>
-static __device__ __noinline__ void admm_chain(const Prob& p, const AdmmScr& sc, double* sm, const AdmmSmem& s, int nchain) {
+static __device__ __noinline__ void admm_chain(const Prob& p, const AdmmScr& sc, double* sm, const AdmmSmem& s, int nchain,
+                                               int ns, ChainSeq& cs) {
   extern __shared__ __align__(16) double sm_admm[];
   sm = sm_admm;
   const int tid = threadIdx.x;
   if (tid >= nchain) return;
-  constexpr int KP = (NX + 7) / 8, PF = 2;
+  constexpr int KP = (NX + 7) / 8, SD = admm_chain_stage<NX>();
   const int T = p.T, i = tid >> 2, q = tid & 3;
   const bool valid = i < NX;
   const int ic = valid ? i : 0;
   const double* M = BWD ? sc.acl : sc.aclr;
   double* vb = sm + s.vb;
-  double2 mreg[PF][KP];
-  double add0[PF], add1[PF];
+  double* ring = sm + s.ws0;   /* the knot-parallel phases' per-warp area is idle during a chain */
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sm + s.cbars);
   auto knot_of = [&](int st) { return BWD ? T - 1 - st : st; };
-  auto load = [&](auto SLOT, int st) {
-    constexpr int sl = decltype(SLOT)::value;
-    const int t = knot_of(st);
-    const double* row = M + (size_t)t * NX * NX + (size_t)ic * NX;
-#pragma unroll
-    for (int m = 0; m < KP; ++m) {
-      const int k = 2 * q + 8 * m;
-      mreg[sl][m] = (k < NX) ? *reinterpret_cast<const double2*>(row + k) : make_double2(0.0, 0.0);
-    }
-    add0[sl] = 0.0; add1[sl] = 0.0;
-    if (q == 0) {
+  /* one elected thread streams step st's operands into ring slot `slot`: the knot's matrix and the
+   * step's additive vectors (BWD: r_t and Vxx_fs_{t-1}; FWD: b_t, which sits in the dx~_{t+1} slot) */
+  int islot = cs.slot;
+  auto issue = [&](int st) {
+    if (tid == 0) {
+      const int t = knot_of(st);
+      double* dst = ring + (size_t)islot * SD;
+      uint64_t* bar = bars + islot;
+      const bool two = BWD && t > 0;
+      mbar_expect_tx(bar, (uint32_t)(NX * NX + NX + (two ? NX : 0)) * 8u);
+      tma_bulk_g2s(dst, M + (size_t)t * NX * NX, NX * NX * 8, bar);
       if (BWD) {
-        add0[sl] = sc.rv[(size_t)t * NX + ic];
-        add1[sl] = t > 0 ? p.Vxx_fs[(size_t)(t - 1) * NX + ic] : 0.0;
+        tma_bulk_g2s(dst + NX * NX, sc.rv + (size_t)t * NX, NX * 8, bar);
+        if (two) tma_bulk_g2s(dst + NX * NX + NX, p.Vxx_fs + (size_t)(t - 1) * NX, NX * 8, bar);
       } else {
-        add0[sl] = p.dxt[(size_t)(t + 1) * NX + ic];
+        tma_bulk_g2s(dst + NX * NX, p.dxt + (size_t)(t + 1) * NX, NX * 8, bar);
       }
     }
+    if (++islot == ns) islot = 0;
   };
+  for (int st = 0; st < ns && st < T; ++st) issue(st);
   if (tid < NX) vb[tid] = BWD ? sc.tv[(size_t)(T - 1) * NX + tid] : p.dxt[tid];
-  load(std::integral_constant<int, 0>{}, 0);
-  if (T > 1) load(std::integral_constant<int, 1>{}, 1);
   named_bar_sync(1, nchain);
-  auto step = [&](auto SLOT, int st) {
-    constexpr int sl = decltype(SLOT)::value;
+  int wslot = cs.slot;
+  uint32_t wphase = cs.phase;
+  for (int st = 0; st < T; ++st) {
     const int t = knot_of(st);
     const double* v = vb + (st & 1) * NX;
     double* vn = vb + ((st + 1) & 1) * NX;
+    mbar_wait(bars + wslot, wphase);
+    const double* stg = ring + (size_t)wslot * SD;
+    const double* row = stg + ic * NX;
     double a0 = 0.0, a1 = 0.0;
 #pragma unroll
     for (int m = 0; m < KP; ++m) {
       const int k = 2 * q + 8 * m;
       if (k < NX) {
+        const double2 mv = *reinterpret_cast<const double2*>(row + k);
         const double2 vv = *reinterpret_cast<const double2*>(v + k);
-        a0 = fma(mreg[sl][m].x, vv.x, a0);
-        a1 = fma(mreg[sl][m].y, vv.y, a1);
+        a0 = fma(mv.x, vv.x, a0);
+        a1 = fma(mv.y, vv.y, a1);
       }
     }
     double acc = a0 + a1;
     acc += __shfl_xor_sync(MG_FULLMASK, acc, 1);
     acc += __shfl_xor_sync(MG_FULLMASK, acc, 2);
-    const double c0 = add0[sl], c1 = add1[sl];
-    if (st + PF < T) load(SLOT, st + PF);
     if (valid && q == 0) {
+      const double c0 = stg[NX * NX + i];
       if (BWD) {
         const double vx = c0 + acc;
         p.Vx[(size_t)t * NX + i] = vx;
         if (t > 0) {
-          const double tn = vx + c1;
+          const double tn = vx + stg[NX * NX + NX + i];
           sc.tv[(size_t)(t - 1) * NX + i] = tn;
           vn[i] = tn;
         }
@@ -344,45 +382,95 @@ static __device__ __noinline__ void admm_chain(const Prob& p, const AdmmScr& sc,
         vn[i] = xn;
       }
     }
-    named_bar_sync(1, nchain);
-  };
-  for (int st = 0; st < T; st += PF) {
-    step(std::integral_constant<int, 0>{}, st);
-    if (st + 1 < T) step(std::integral_constant<int, 1>{}, st + 1);
+    if (++wslot == ns) { wslot = 0; wphase ^= 1u; }
+    named_bar_sync(1, nchain);   /* step st complete: its slot is free, v_{st+1} visible */
+    if (st + ns < T) issue(st + ns);
   }
+  cs.slot = wslot;
+  cs.phase = wphase;
 }
 
 /* --------------------------------------------- gains and b_t after the backward chain */
+/* Per-warp TMA stage of the knot-parallel phases (STAGED shapes): lane 0 pulls the knot's matrix
+ * blocks into the warp's shared-memory stage with bulk copies that complete on the warp's
+ * mbarrier; `seq` counts the loads of this warp (phase parity), it persists across phases. */
+struct WarpStage {
+  uint64_t* bar;
+  double* buf;
+  uint32_t seq;
+  __device__ __forceinline__ void begin(uint32_t bytes, int lane) { if (lane == 0) mbar_expect_tx(bar, bytes); }
+  __device__ __forceinline__ void copy(int off, const double* src, int ndoubles, int lane) {
+    if (lane == 0 && ndoubles > 0) tma_bulk_g2s(buf + off, src, (uint32_t)ndoubles * 8u, bar);
+  }
+  __device__ __forceinline__ void wait() { mbar_wait(bar, seq & 1u); ++seq; }
+};
+
 /* Qu_t = qu_t + Fu_t^T tmp_t, k_t = Quu_t^-1 Qu_t (src/csqp.cpp:1083-1097), b_t = fs_{t+1} - Fu_t k_t;
  * one warp per knot.  qu_t was left in the Qu_ slot by admm_update. */
-template <int NX, int NU>
-static __device__ __noinline__ void admm_gains(const Prob& p, const AdmmScr& sc, double* sm, const AdmmSmem& s) {
+template <int NX, int NU, bool STAGED>
+static __device__ __noinline__ void admm_gains(const Prob& p, const AdmmScr& sc, double* sm, const AdmmSmem& s,
+                                               uint32_t& wseq) {
   extern __shared__ __align__(16) double sm_admm[];
   sm = sm_admm;
   using W = AdmmWs<NX, NU>;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
   double* ws = sm + s.ws0 + warp * s.wsn;
   double *xs = ws + W::xs, *us = ws + W::us, *qu = ws + W::qu;
+  WarpStage stg{reinterpret_cast<uint64_t*>(sm + s.wbars) + warp, ws + s.stg, wseq};
+  auto pull = [&](int t) { /* knot t's blocks and vectors -> L2 */
+    if (t >= p.T) return;
+    pf_block(p.Fu + (size_t)t * NX * NU, NX * NU, lane);
+    pf_block(p.L + (size_t)t * NU * NU, NU * NU, lane - 1);
+    pf_vec(sc.tv + (size_t)t * NX, NX, lane - 2);
+    pf_vec(p.fs + (size_t)(t + 1) * NX, NX, lane - 10);
+    pf_vec(p.Qu + (size_t)t * NU, NU, lane - 18);
+  };
+  pull(warp + nw);
   for (int t = warp; t < p.T; t += nw) {
     const double* Fu = p.Fu + (size_t)t * NX * NU;
-    for (int i = lane; i < NX; i += 32) xs[i] = sc.tv[(size_t)t * NX + i];
+    const double* L = p.L + (size_t)t * NU * NU;
+    if constexpr (STAGED) {
+      stg.begin((uint32_t)(NX * NU + NU * NU) * 8u, lane);
+      stg.copy(0, Fu, NX * NU, lane);
+      stg.copy(NX * NU, L, NU * NU, lane);
+    }
+    pull(t + 2 * nw);
+    /* the knot's vectors: all loads in flight at once */
+    double tv0 = 0.0, tv1 = 0.0, fs0 = 0.0, fs1 = 0.0, quv = 0.0;
+    if (lane < NX) { tv0 = sc.tv[(size_t)t * NX + lane]; fs0 = p.fs[(size_t)(t + 1) * NX + lane]; }
+    if (NX > 32 && lane + 32 < NX) { tv1 = sc.tv[(size_t)t * NX + lane + 32]; fs1 = p.fs[(size_t)(t + 1) * NX + lane + 32]; }
+    if (lane < NU) quv = p.Qu[(size_t)t * NU + lane];
+    if (lane < NX) xs[lane] = tv0;
+    if (NX > 32 && lane + 32 < NX) xs[lane + 32] = tv1;
+    if (NX > 64) for (int i = lane + 64; i < NX; i += 32) xs[i] = sc.tv[(size_t)t * NX + i];
+    if (lane < NU) qu[lane] = quv;
+    if constexpr (STAGED) stg.wait();
     __syncwarp();
-    wdot4<NX>(Fu, NU, xs, lane, [&](int a, double acc) {
-      double v = p.Qu[(size_t)t * NU + a];
-      v += acc;
-      qu[a] = v;
-      p.Qu[(size_t)t * NU + a] = v;
-    });
-    __syncwarp();
-    double ki = (lane < NU) ? qu[lane] : 0.0;
-    ki = wsolve_llt<NU>(p.L + (size_t)t * NU * NU, ki, lane);
-    if (lane < NU) { us[lane] = ki; p.kff[(size_t)t * NU + lane] = ki; }
-    __syncwarp();
-    waxpy<NX, NU>(Fu, us, lane, [&](int i, double acc) {
-      p.dxt[(size_t)(t + 1) * NX + i] = p.fs[(size_t)(t + 1) * NX + i] - acc;
-    });
+    auto body = [&](const double* mFu, const double* mL) {
+      wdot4<NX>(mFu, NU, xs, lane, [&](int a, double acc) {
+        double v = qu[a];
+        v += acc;
+        us[a] = v;                      /* Qu_t (us doubles as its buffer until the solve) */
+        p.Qu[(size_t)t * NU + a] = v;
+      });
+      __syncwarp();
+      double ki = (lane < NU) ? us[lane] : 0.0;
+      ki = wsolve_llt<NU>(mL, ki, lane);
+      __syncwarp();
+      if (lane < NU) { us[lane] = ki; p.kff[(size_t)t * NU + lane] = ki; }
+      __syncwarp();
+      waxpy<NX, NU>(mFu, us, lane, [&](int i, double acc) {
+        /* the lane that owns row i also loaded fs_{t+1}[i] */
+        const double f = (i < 32) ? fs0 : (i < 64) ? fs1 : p.fs[(size_t)(t + 1) * NX + i];
+        p.dxt[(size_t)(t + 1) * NX + i] = f - acc;
+      });
+    };
+    if constexpr (STAGED) body(stg.buf, stg.buf + NX * NU);
+    else body(Fu, L);
     __syncwarp();
   }
+  wseq = stg.seq;
+  fence_proxy_async(); /* b_t -> the forward chain's TMA */
 }
 
 /* ------------------------------- du~, update_lagrangian_parameters, r_t of the next sweep */
@@ -390,9 +478,10 @@ static __device__ __noinline__ void admm_gains(const Prob& p, const AdmmScr& sc,
  * 1241-1242); c = Gx dx~ + Gu du~, z_relaxed, z, y (:1229-1239); the residual norms on check
  * iterations (:1244-1278); and, when the next backward sweep is a light one, its knot-local terms
  * qu_t (left in the Qu_ slot) and r_t = qx_t - K_t^T qu_t (src/csqp.cpp:1068-1104 regrouped). */
-template <int NX, int NU>
+template <int NX, int NU, bool STAGED>
 static __device__ __noinline__ void admm_update(const Prob& p, const AdmmScr& sc, double* sm, const AdmmSmem& s,
-                                                const mimgpu_csqp_params& q_, int iter, bool need_r, AdmmNorms& n) {
+                                                const mimgpu_csqp_params& q_, int iter, bool need_r, bool stage_g,
+                                                AdmmNorms& n, uint32_t& wseq) {
   extern __shared__ __align__(16) double sm_admm[];
   sm = sm_admm;
   using W = AdmmWs<NX, NU>;
@@ -402,20 +491,19 @@ static __device__ __noinline__ void admm_update(const Prob& p, const AdmmScr& sc
   double* ws = sm + s.ws0 + warp * s.wsn;
   double *xs = ws + W::xs, *us = ws + W::us, *sqx = ws + W::qx, *squ = ws + W::qu, *sd = ws + W::ds, *se1 = sd + ngm,
          *se2 = se1 + ngm;
+  WarpStage stg{reinterpret_cast<uint64_t*>(sm + s.wbars) + warp, ws + s.stg, wseq};
   const bool check = (iter % q_.rho_update_interval) == 0;
   const bool heur = q_.update_rho_with_heuristic != 0;
   const bool dualg = check && !heur;
   const double alpha = q_.alpha, sigma = q_.sigma;
   double np_ = -CUDART_INF, nd_ = -CUDART_INF, npr = -CUDART_INF, ndr = -CUDART_INF; /* src/csqp.cpp:1201-1204 */
 
-  /* rows r of one knot: c given, z / y projection and the row-local norms; returns d_r */
-  auto project = [&](size_t o, int r, double c, const double* g, const double* lb, const double* ub) {
-    const double zp = p.z[o + r];
+  /* row r of one knot: c given, z / y projection and the row-local norms (src/csqp.cpp:1231-1239) */
+  auto project = [&](size_t o, int r, double c, double zp, double rho, double yo, double lo, double hi) {
     double zr = alpha * c;
     zr += (1. - alpha) * zp;
-    const double rho = p.rho[o + r], irho = 1. / rho, yo = p.y[o + r];
+    const double irho = 1. / rho;
     double z = zr + yo * irho;
-    const double lo = lb[r] - g[r], hi = ub[r] - g[r];
     z = (z < lo) ? lo : z;
     z = (hi < z) ? hi : z;
     const double yn = yo + rho * (zr - z);
@@ -435,20 +523,80 @@ static __device__ __noinline__ void admm_update(const Prob& p, const AdmmScr& sc
       }
     }
   };
-
+  auto pull = [&](int t) { /* running knot t's blocks and vectors -> L2 */
+    if (t >= T) return;
+    pf_block(p.K + (size_t)t * NX * NU, NX * NU, lane);
+    if (ng) {
+      pf_block(p.Gx + (size_t)t * ng * NX, ng * NX, lane - 1);
+      pf_block(p.Gu + (size_t)t * ng * NU, ng * NU, lane - 2);
+      const size_t o = (size_t)t * ng;
+      pf_vec(p.y + o, ng, lane - 3); pf_vec(p.z + o, ng, lane - 3); pf_vec(p.rho + o, ng, lane - 3);
+      pf_vec(p.g + o, ng, lane - 3); pf_vec(p.glb + o, ng, lane - 3); pf_vec(p.gub + o, ng, lane - 3);
+    }
+    pf_vec(p.dxt + (size_t)t * NX, NX, lane - 11);
+    pf_vec(p.kff + (size_t)t * NU, NU, lane - 19);
+    if (need_r) { pf_vec(p.Lx + (size_t)t * NX, NX, lane - 11); pf_vec(p.Lu + (size_t)t * NU, NU, lane - 19); }
+  };
+  pull(warp + nw);
   for (int t = warp; t <= T; t += nw) {
     const bool last = (t == T);
     const int nc = last ? ngT : ng;
-    for (int i = lane; i < NX; i += 32) {
-      const double x = p.dxt[(size_t)t * NX + i];
-      xs[i] = x;
-      p.dx[(size_t)t * NX + i] = x;
+    const size_t o = (size_t)t * ng;
+    const double* Kg = p.K + (size_t)(last ? 0 : t) * NX * NU;
+    const double* Gxg = last ? p.GxT : (ng ? p.Gx + (size_t)t * ng * NX : nullptr);
+    const double* Gug = (last || !ng) ? nullptr : p.Gu + (size_t)t * ng * NU;
+    const bool sg = STAGED && stage_g && !last && ng > 0;
+    if constexpr (STAGED) {
+      if (!last) {
+        stg.begin((uint32_t)(NX * NU + (sg ? ng * (NX + NU) : 0)) * 8u, lane);
+        stg.copy(0, Kg, NX * NU, lane);
+        if (sg) { stg.copy(NX * NU, Gxg, ng * NX, lane); stg.copy(NX * NU + ng * NX, Gug, ng * NU, lane); }
+      }
     }
+    pull(t + 2 * nw);
+    /* the knot's vectors: every load in flight before the first use */
+    double x0 = 0.0, x1 = 0.0, kf = 0.0, lx0 = 0.0, lx1 = 0.0, luv = 0.0;
+    double zp = 0.0, rho = 1.0, yo = 0.0, lo = 0.0, hi = 0.0;
+    const bool rowreg = nc > 0 && nc <= 32;   /* lane r holds row r's vectors */
+    if (lane < NX) x0 = p.dxt[(size_t)t * NX + lane];
+    if (NX > 32 && lane + 32 < NX) x1 = p.dxt[(size_t)t * NX + lane + 32];
+    if (!last && lane < NU) kf = p.kff[(size_t)t * NU + lane];
+    if (rowreg && lane < nc) {
+      const double* g = last ? p.gT : p.g + o;
+      const double* lb = last ? p.glbT : p.glb + o;
+      const double* ub = last ? p.gubT : p.gub + o;
+      zp = p.z[o + lane]; rho = p.rho[o + lane]; yo = p.y[o + lane];
+      const double gv = g[lane];
+      lo = lb[lane] - gv; hi = ub[lane] - gv;
+    }
+    if (need_r && !last) {
+      if (lane < NX) lx0 = p.Lx[(size_t)t * NX + lane];
+      if (NX > 32 && lane + 32 < NX) lx1 = p.Lx[(size_t)t * NX + lane + 32];
+      if (lane < NU) luv = p.Lu[(size_t)t * NU + lane];
+    }
+    if (lane < NX) { xs[lane] = x0; p.dx[(size_t)t * NX + lane] = x0; }
+    if (NX > 32 && lane + 32 < NX) { xs[lane + 32] = x1; p.dx[(size_t)t * NX + lane + 32] = x1; }
+    if (NX > 64)
+      for (int i = lane + 64; i < NX; i += 32) { const double x = p.dxt[(size_t)t * NX + i]; xs[i] = x; p.dx[(size_t)t * NX + i] = x; }
+    if (need_r && !last) { /* qx_t / qu_t start from Lx - sigma dx~ and Lu (the G^T d and -sigma du~ terms follow) */
+      if (lane < NX) sqx[lane] = lx0;
+      if (NX > 32 && lane + 32 < NX) sqx[lane + 32] = lx1;
+      if (NX > 64) for (int i = lane + 64; i < NX; i += 32) sqx[i] = p.Lx[(size_t)t * NX + i];
+      if (lane < NU) squ[lane] = luv;
+    }
+    if (!last && lane < NU) us[lane] = kf;    /* k_t, replaced by du~_t below */
+    if constexpr (STAGED) { if (!last) stg.wait(); }
     __syncwarp();
-    if (!last) {
-      const double* K = p.K + (size_t)t * NX * NU;
+    const double* K = Kg;
+    const double* Gx = Gxg;
+    const double* Gu = Gug;
+    if constexpr (STAGED) {
+      if (!last) K = stg.buf;
+      if (sg) { Gx = stg.buf + NX * NU; Gu = Gx + ng * NX; }
+    }
+    if (!last) { /* du~ = -k - K dx~ (src/csqp.cpp:636-637); us[a] holds k_t[a] and is replaced by du~_t[a] */
       wdot4<NX>(K, NU, xs, lane, [&](int a, double acc) {
-        double u = -p.kff[(size_t)t * NU + a];
+        double u = -us[a];
         u -= acc;
         us[a] = u;
         p.dut[(size_t)t * NU + a] = u;
@@ -456,24 +604,32 @@ static __device__ __noinline__ void admm_update(const Prob& p, const AdmmScr& sc
       });
       __syncwarp();
     }
-    const double* Gx = last ? p.GxT : (ng ? p.Gx + (size_t)t * ng * NX : nullptr);
-    const double* Gu = (last || !ng) ? nullptr : p.Gu + (size_t)t * ng * NU;
-    const size_t o = (size_t)t * ng;
     if (nc) {
       /* c_r = sum_j Gx[r][j] dx~[j] + sum_a Gu[r][a] du~[a]: lanes over rows, columns split over lane groups */
       const int np2 = nc <= 4 ? 4 : nc <= 8 ? 8 : nc <= 16 ? 16 : 32, ph_n = 32 / np2;
       const int rl = lane % np2, ph = lane / np2;
-      const double* g = last ? p.gT : p.g + o;
-      const double* lb = last ? p.glbT : p.glb + o;
-      const double* ub = last ? p.gubT : p.gub + o;
       for (int r0 = 0; r0 < nc; r0 += np2) {
         const int r = r0 + rl;
         const bool valid = r < nc;
         const int rc = valid ? r : 0;
-        double a1 = 0.0, a2 = 0.0;
-        for (int j = ph; j < NX; j += ph_n) a1 = fma(Gx[rc + nc * j], xs[j], a1);
-        if (Gu)
-          for (int a = ph; a < NU; a += ph_n) a2 = fma(Gu[rc + nc * a], us[a], a2);
+        double a1 = 0.0, a2 = 0.0, b1 = 0.0, b2 = 0.0;
+        int j = ph;
+        for (; j + ph_n < NX; j += 2 * ph_n) {
+          const double g0 = Gx[rc + nc * j], g1 = Gx[rc + nc * (j + ph_n)];
+          a1 = fma(g0, xs[j], a1);
+          b1 = fma(g1, xs[j + ph_n], b1);
+        }
+        if (j < NX) a1 = fma(Gx[rc + nc * j], xs[j], a1);
+        if (Gu) {
+          int a = ph;
+          for (; a + ph_n < NU; a += 2 * ph_n) {
+            const double g0 = Gu[rc + nc * a], g1 = Gu[rc + nc * (a + ph_n)];
+            a2 = fma(g0, us[a], a2);
+            b2 = fma(g1, us[a + ph_n], b2);
+          }
+          if (a < NU) a2 = fma(Gu[rc + nc * a], us[a], a2);
+        }
+        a1 += b1; a2 += b2;
         for (int off = np2; off < 32; off <<= 1) {
           a1 += __shfl_xor_sync(MG_FULLMASK, a1, off);
           a2 += __shfl_xor_sync(MG_FULLMASK, a2, off);
@@ -482,7 +638,14 @@ static __device__ __noinline__ void admm_update(const Prob& p, const AdmmScr& sc
           double c = 0.0;
           c += a1;
           c += a2;
-          project(o, r, c, g, lb, ub);
+          if (rowreg) {
+            project(o, r, c, zp, rho, yo, lo, hi);
+          } else {
+            const double* g = last ? p.gT : p.g + o;
+            const double* lb = last ? p.glbT : p.glb + o;
+            const double* ub = last ? p.gubT : p.gub + o;
+            project(o, r, c, p.z[o + r], p.rho[o + r], p.y[o + r], lb[r] - g[r], ub[r] - g[r]);
+          }
         }
       }
       __syncwarp();
@@ -513,7 +676,7 @@ static __device__ __noinline__ void admm_update(const Prob& p, const AdmmScr& sc
                   [&](int i, double s0, double s1, double s2) {
                     if (dualg) { nd_ = nmax(nd_, fabs(s1)); ndr = nmax(ndr, fabs(s2)); }
                     if (need_r) {
-                      double v = p.Lx[(size_t)t * NX + i];
+                      double v = sqx[i];
                       v -= sigma * xs[i];
                       if (gx_d) v += s0;
                       sqx[i] = v;
@@ -523,7 +686,7 @@ static __device__ __noinline__ void admm_update(const Prob& p, const AdmmScr& sc
                   [&](int a, double s0, double s1, double s2) {
                     if (dualg) { nd_ = nmax(nd_, fabs(s1)); ndr = nmax(ndr, fabs(s2)); }
                     if (need_r) {
-                      double v = p.Lu[(size_t)t * NU + a];
+                      double v = squ[a];
                       v -= sigma * us[a];
                       v += s0;
                       squ[a] = v;
@@ -531,21 +694,22 @@ static __device__ __noinline__ void admm_update(const Prob& p, const AdmmScr& sc
                     }
                   });
       } else if (need_r) {
-        for (int i = lane; i < NX; i += 32) sqx[i] = p.Lx[(size_t)t * NX + i] - sigma * xs[i];
+        for (int i = lane; i < NX; i += 32) sqx[i] -= sigma * xs[i];
         for (int a = lane; a < NU; a += 32) {
-          const double v = p.Lu[(size_t)t * NU + a] - sigma * us[a];
+          const double v = squ[a] - sigma * us[a];
           squ[a] = v;
           p.Qu[(size_t)t * NU + a] = v;
         }
       }
       __syncwarp();
       if (need_r) { /* r_t = qx_t - K_t^T qu_t; K row-major NU x NX = col-major NX x NU */
-        waxpy<NX, NU>(p.K + (size_t)t * NX * NU, squ, lane,
-                      [&](int i, double acc) { sc.rv[(size_t)t * NX + i] = sqx[i] - acc; });
+        waxpy<NX, NU>(K, squ, lane, [&](int i, double acc) { sc.rv[(size_t)t * NX + i] = sqx[i] - acc; });
       }
-      __syncwarp();
     }
+    __syncwarp();
   }
+  wseq = stg.seq;
+  fence_proxy_async(); /* r_t -> the backward chain's TMA */
   /* src/csqp.cpp:1201-1204: the four norms are -inf unless this is a check iteration */
   n.primal = n.dual = n.primal_rel = n.dual_rel = -CUDART_INF;
   if (check) {
@@ -565,9 +729,14 @@ static __device__ __noinline__ void admm_update(const Prob& p, const AdmmScr& sc
 /* ------------------------------------------------------------------ the kernel */
 struct AdmmKPar {
   mimgpu_csqp_params q;
-  int with_kkt, ric_total, nchain, dbg;
+  int with_kkt, ric_total, nchain, stage_g, chain_ns;
   double *acl, *aclr, *rv, *tv; /* [B][T][...] scratch of the condensed iterations */
 };
+
+/* shapes whose knot blocks go through a per-warp TMA stage in the knot-parallel phases (the
+ * larger ones read global memory directly: their blocks do not fit one stage per warp) */
+template <int NX, int NU>
+__host__ __device__ constexpr bool admm_staged() { return NX <= 36; }
 
 template <int NX, int NU> struct AdmmTune { static constexpr int MAXT = NX <= 16 ? 128 : 256, MINB = NX <= 16 ? 6 : 2; };
 template <> struct AdmmTune<36, 12> { static constexpr int MAXT = 192, MINB = 2; };
@@ -596,7 +765,9 @@ k_csqp_direction_admm(KArgs a, AdmmKPar kp) {
   const int b = a.active ? a.active[blockIdx.x] : (int)blockIdx.x;
   Prob p = bind(a, b);
   const int nw = blockDim.x >> 5;
-  const AdmmSmem ss = admm_layout<NX, NU>(p.ng, p.ngT, nw, kp.ric_total);
+  constexpr bool STAGED = admm_staged<NX, NU>();
+  const AdmmSmem ss = admm_layout<NX, NU>(p.ng, p.ngT, nw, kp.ric_total,
+                                          admm_stage_doubles<NX, NU>(p.ng, STAGED, kp.stage_g != 0));
   double* sm = sm_admm;
   double* gsm = sm + ss.uni; /* Riccati layouts live in the union region */
   const Smem gs = smem_layout(NX, NU, p.ng, p.ngT, a.stage_fx);
@@ -607,9 +778,13 @@ k_csqp_direction_admm(KArgs a, AdmmKPar kp) {
   if (threadIdx.x == 0) {
     mbar_init(ric_bars, 1);
     mbar_init(ric_bars + 1, 1);
+    for (int w = 0; w < nw; ++w) mbar_init(reinterpret_cast<uint64_t*>(sm + ss.wbars) + w, 1);
+    for (int w = 0; w < 8; ++w) mbar_init(reinterpret_cast<uint64_t*>(sm + ss.cbars) + w, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
+  uint32_t wseq = 0u; /* loads this warp has put through its TMA stage */
+  ChainSeq cseq{0, 0u};  /* ring position of the chains' TMA pipeline */
   AdmmScr sc;
   {
     const size_t sb = (size_t)b * p.T;
@@ -649,15 +824,15 @@ k_csqp_direction_admm(KArgs a, AdmmKPar kp) {
         __syncthreads();
         admm_post_full<NX, NU>(p, sc, sm, ss);
       } else {
-        admm_chain<NX, true>(p, sc, sm, ss, kp.nchain);
+        admm_chain<NX, true>(p, sc, sm, ss, kp.nchain, kp.chain_ns, cseq);
         __syncthreads();
-        admm_gains<NX, NU>(p, sc, sm, ss);
+        admm_gains<NX, NU, STAGED>(p, sc, sm, ss, wseq);
       }
       __syncthreads();
-      admm_chain<NX, false>(p, sc, sm, ss, kp.nchain);
+      admm_chain<NX, false>(p, sc, sm, ss, kp.nchain, kp.chain_ns, cseq);
       __syncthreads();
       const bool need_r = (it + 1 < q.max_qp_iters + 1) && !is_full(it + 1);
-      admm_update<NX, NU>(p, sc, sm, ss, q, it, need_r, n);
+      admm_update<NX, NU, STAGED>(p, sc, sm, ss, q, it, need_r, kp.stage_g != 0, n, wseq);
       if (it % interval == 0) {
         /* update_rho_vec (src/csqp.cpp:519-532) */
         const double scale = sqrt((n.primal * n.dual_rel) / (n.dual * n.primal_rel));
@@ -709,9 +884,25 @@ static AdmmPlan admm_plan_t(const mimgpu_shape& sh, int stage_fx, int max_smem) 
         if (rs.total > ric_total) ric_total = rs.total;
       }
     }
-    const AdmmSmem ss = admm_layout<NX, NU>(sh.ng, sh.ngT, pl.nt / 32, ric_total);
+    /* stage Gx / Gu next to K only while MINB CTAs of this size still share an SM */
+    constexpr bool STAGED = admm_staged<NX, NU>();
+    int stage_g = STAGED ? 1 : 0;
+    AdmmSmem ss = admm_layout<NX, NU>(sh.ng, sh.ngT, pl.nt / 32, ric_total, admm_stage_doubles<NX, NU>(sh.ng, STAGED, true));
+    if (stage_g && AdmmTune<NX, NU>::MINB * (ss.total * 8 + 1024) > 233472) {
+      stage_g = 0;
+      ss = admm_layout<NX, NU>(sh.ng, sh.ngT, pl.nt / 32, ric_total, admm_stage_doubles<NX, NU>(sh.ng, STAGED, false));
+    }
+    /* TMA ring of the chains: as many [Acl | add0 | add1] stages as the union region holds */
+    auto ring_ns = [&](const AdmmSmem& L) { int n = (L.total - L.ws0) / admm_chain_stage<NX>(); return n > 8 ? 8 : n; };
+    if (ring_ns(ss) < 3) { /* grow the union region to three stages */
+      const int need = 2 * NX + 3 * admm_chain_stage<NX>();
+      if (need > ric_total) ric_total = need;
+      ss = admm_layout<NX, NU>(sh.ng, sh.ngT, pl.nt / 32, ric_total, admm_stage_doubles<NX, NU>(sh.ng, STAGED, stage_g != 0));
+    }
     const int bytes = ss.total * 8;
     if (bytes > max_smem) continue;
+    pl.stage_g = stage_g;
+    pl.chain_ns = ring_ns(ss);
     cudaError_t e;
     if (mma) {
       if constexpr (MMA) e = cudaFuncSetAttribute(k_csqp_direction_admm<NX, NU, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
@@ -741,7 +932,7 @@ static inline AdmmPlan admm_plan(const mimgpu_shape& sh, int stage_fx, int max_s
 static inline int admm_csqp_launch(const KArgs& a, const mimgpu_csqp_params& q, int with_kkt, const AdmmPlan& pl,
                                    double* const scratch[4], cudaStream_t st) {
   AdmmKPar kp;
-  kp.q = q; kp.with_kkt = with_kkt; kp.ric_total = pl.ric_total; kp.nchain = pl.nchain; kp.dbg = 0;
+  kp.q = q; kp.with_kkt = with_kkt; kp.ric_total = pl.ric_total; kp.nchain = pl.nchain; kp.stage_g = pl.stage_g; kp.chain_ns = pl.chain_ns;
   kp.acl = scratch[0]; kp.aclr = scratch[1]; kp.rv = scratch[2]; kp.tv = scratch[3];
 #define X(NX_, NU_)                                                                                         \
   if (a.sh.nx == NX_ && a.sh.nu == NU_) {                                                                   \

@@ -14,7 +14,7 @@ struct StreamPlan {
   int ok, ns, nt, smem_bytes, generic_total, direct;
 };
 struct AdmmPlan {
-  int ok, nt, smem_bytes, ric_total, nchain, use_mma;
+  int ok, nt, smem_bytes, ric_total, nchain, use_mma, stage_g, chain_ns;
 };
 struct CtaPlan {
   int ok, nt, smem_bytes, nbuf, ns;

@@ -219,7 +219,8 @@ def test_gpu_knot_records_layout(eng, oracle_lib):
     assert b.launch_count - l0 == 1, "records path must not launch a re-layout kernel"
     for n in ("dx", "du", "lag_mul", "K", "Vxx"):
         assert np.array_equal(b.field(n), ref[n]), n
-    assert np.array_equal(b.scalar("KKT"), kkt) and np.array_equal(b.scalar("merit"), a.scalar("merit"))
+    assert np.array_equal(b.scalar("KKT"), kkt), np.abs(b.scalar("KKT") - kkt).max()
+    assert np.array_equal(b.scalar("merit"), a.scalar("merit")), (b.scalar("merit")[:4], a.scalar("merit")[:4], cost[:4])
     for n in ("Qu", "Quu_llt"):   # full-spill recomputation needs the field-major arrays: rebuilt on demand
         assert np.array_equal(b.field(n), ref[n]), n
     # device-attached records, mutated in place between two calls
