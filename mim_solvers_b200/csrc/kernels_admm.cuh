@@ -30,8 +30,8 @@
  * 1e-14 relative after 25 iterations on every BASELINE shape; parity bar 1e-9).
  *
  * Full sweeps (iteration k = 1 mod interval, src/csqp.cpp:477) keep the Riccati code of
- * kernels_ric.cuh (DMMA) / kernels_generic.cuh; right after one, Acl_t (both orientations) and
- * b_t are rebuilt from the fresh K_t, k_t.
+ * kernels_ric.cuh (DMMA) / kernels_generic.cuh; right after one, Acl_t and b_t are rebuilt from the
+ * fresh K_t, k_t.
  */
 #pragma once
 #include <cuda_runtime.h>
@@ -55,18 +55,18 @@ struct AdmmSmem {
 template <int NX, int NU>
 __host__ __device__ inline int admm_stage_doubles(int ng, bool staged, bool stage_g) {
   if (!staged) return 0;
-  const int a = NX * NU + (stage_g ? ng * (NX + NU) : 0), b = NX * NU + NU * NU;
-  return a > b ? a : b;
+  const int gb = stage_g ? ng * (NX + NU) : 0, lb = NU * NU;   /* B buffer: [Gx Gu] (update) | LLT (gains) */
+  return 2 * NX * NU + (gb > lb ? gb : lb);
 }
 template <int NX, int NU>
 __host__ __device__ inline AdmmSmem admm_layout(int ng, int ngT, int nwarps, int ric_total, int stage_doubles) {
   AdmmSmem s;
   const int ngm = ng > ngT ? ng : ngT;
   s.bars = 0;                         /* two mbarriers of the Riccati sweep */
-  s.wbars = 8;                        /* one mbarrier per warp (TMA stage of the knot-parallel phases) */
-  s.cbars = 8 + 16;                   /* up to eight mbarriers of the chains' TMA ring */
-  s.red = 8 + 16 + 8;
-  s.uni = 8 + 16 + 8 + 64;
+  s.wbars = 8;                        /* three mbarriers per warp (pipeline of the knot-parallel phases) */
+  s.cbars = 8 + 48;                   /* full[8] + empty[8] mbarriers of the chains' TMA ring */
+  s.red = 8 + 48 + 16;
+  s.uni = 8 + 48 + 16 + 64;
   s.vb = s.uni;                       /* chain vector, double buffered */
   s.ws0 = s.uni + 2 * NX;             /* per-warp scratch + stage of the knot-parallel phases */
   s.stg = (2 * NX + 2 * NU + 3 * ngm + 1) & ~1;
@@ -113,9 +113,10 @@ __device__ __forceinline__ void wdot4(const double* M, int nrows, const double* 
 
 /* Columns of a run-time-tall matrix against up to three vectors at once:
  * s_e[o] = sum_r M[r + nin * o] v_e[r], o < nrows (column o of a col-major nin x nrows block).
- * Vectors that are null are skipped.  f(o, s0, s1, s2) runs on one lane per column. */
-template <class F>
-__device__ __forceinline__ void wdot4_rt3(const double* M, int nrows, int nin, const double* v0, const double* v1,
+ * U0: v0 takes part; U12: v1 and v2 take part (check iterations).  f(o, s0, s1, s2) runs on one
+ * lane per column. */
+template <bool U0, bool U12, class F>
+__device__ __forceinline__ void wdot4_rtv(const double* M, int nrows, int nin, const double* v0, const double* v1,
                                           const double* v2, int lane, F f) {
   const int g = lane >> 2, q = lane & 3;
   for (int o0 = 0; o0 < nrows; o0 += 8) {
@@ -125,18 +126,24 @@ __device__ __forceinline__ void wdot4_rt3(const double* M, int nrows, int nin, c
     double s0 = 0.0, s1 = 0.0, s2 = 0.0;
     for (int r = q; r < nin; r += 4) {
       const double mv = col[r];
-      if (v0) s0 = fma(mv, v0[r], s0);
-      if (v1) s1 = fma(mv, v1[r], s1);
-      if (v2) s2 = fma(mv, v2[r], s2);
+      if (U0) s0 = fma(mv, v0[r], s0);
+      if (U12) { s1 = fma(mv, v1[r], s1); s2 = fma(mv, v2[r], s2); }
     }
 #pragma unroll
     for (int off = 1; off <= 2; off <<= 1) {
-      s0 += __shfl_xor_sync(MG_FULLMASK, s0, off);
-      s1 += __shfl_xor_sync(MG_FULLMASK, s1, off);
-      s2 += __shfl_xor_sync(MG_FULLMASK, s2, off);
+      if (U0) s0 += __shfl_xor_sync(MG_FULLMASK, s0, off);
+      if (U12) { s1 += __shfl_xor_sync(MG_FULLMASK, s1, off); s2 += __shfl_xor_sync(MG_FULLMASK, s2, off); }
     }
     if (valid && q == 0) f(o, s0, s1, s2);
   }
+}
+template <class F>
+__device__ __forceinline__ void wdot4_rt3(const double* M, int nrows, int nin, const double* v0, const double* v1,
+                                          const double* v2, int lane, F f) {
+  if (v0 && v1) wdot4_rtv<true, true>(M, nrows, nin, v0, v1, v2, lane, f);
+  else if (v0) wdot4_rtv<true, false>(M, nrows, nin, v0, v1, v2, lane, f);
+  else if (v1) wdot4_rtv<false, true>(M, nrows, nin, v0, v1, v2, lane, f);
+  else wdot4_rtv<false, false>(M, nrows, nin, v0, v1, v2, lane, f);
 }
 
 /* y[i] = sum_j M[i + NI * j] w[j], i < NI, j < NJ (col-major NI x NJ, lanes walk consecutive i:
@@ -229,14 +236,13 @@ __device__ __forceinline__ void pf_vec(const double* p, int ndoubles, int lane) 
 
 /* ----------------------------------------------------------- per-problem scratch */
 struct AdmmScr {
-  double* acl;   /* [T][NX*NX] Acl_t col-major: column i contiguous -> rows of Acl_t^T */
-  double* aclr;  /* [T][NX*NX] Acl_t row-major: row i contiguous */
+  double* acl;   /* [T][NX*NX] Acl_t col-major */
   double* rv;    /* [T][NX]    r_t */
   double* tv;    /* [T][NX]    tmp_t = Vx_{t+1} + Vxx_fs_t */
 };
 
 /* ------------------------------------------------------ after a full Riccati sweep */
-/* Acl_t = Fx_t - Fu_t K_t in both orientations and b_t = fs_{t+1} - Fu_t k_t (stored in the
+/* Acl_t = Fx_t - Fu_t K_t and b_t = fs_{t+1} - Fu_t k_t (stored in the
  * dx~_{t+1} slot, the forward chain turns it into dx~_{t+1}); one warp per knot. */
 template <int NX, int NU>
 static __device__ __noinline__ void admm_post_full(const Prob& p, const AdmmScr& sc, double* sm, const AdmmSmem& s) {
@@ -250,7 +256,6 @@ static __device__ __noinline__ void admm_post_full(const Prob& p, const AdmmScr&
     const double* Fu = p.Fu + (size_t)t * NX * NU;
     const double* K = p.K + (size_t)t * NX * NU;
     double* A = sc.acl + (size_t)t * NX * NX;
-    double* AR = sc.aclr + (size_t)t * NX * NX;
     /* lanes over rows i: Fu[i][.] in registers, K[.][j] broadcast */
     for (int i0 = 0; i0 < NX; i0 += 32) {
       const int i = i0 + lane;
@@ -264,21 +269,6 @@ static __device__ __noinline__ void admm_post_full(const Prob& p, const AdmmScr&
 #pragma unroll
         for (int a = 0; a < NU; ++a) acc = fma(fu[a], K[a * NX + j], acc);
         if (valid) A[i + NX * j] = Fx[i + NX * j] - acc;
-      }
-    }
-    /* lanes over columns j: K[.][j] in registers, Fu[i][.] broadcast; writes row i contiguously */
-    for (int j0 = 0; j0 < NX; j0 += 32) {
-      const int j = j0 + lane;
-      const bool valid = j < NX;
-      const int jc = valid ? j : 0;
-      double kk[NU];
-#pragma unroll
-      for (int a = 0; a < NU; ++a) kk[a] = K[a * NX + jc];
-      for (int i = 0; i < NX; ++i) {
-        double acc = 0.0;
-#pragma unroll
-        for (int a = 0; a < NU; ++a) acc = fma(Fu[i + NX * a], kk[a], acc);
-        if (valid) AR[i * NX + j] = Fx[i + NX * jc] - acc;
       }
     }
     /* b_t */
@@ -304,172 +294,245 @@ struct ChainSeq {
 template <int NX>
 __host__ __device__ constexpr int admm_chain_stage() { return NX * NX + 2 * NX; } /* [M | add0 | add1] */
 
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+/* Warps [0, nchain / 32) compute (named barrier 1); the NEXT warp is the producer: its lane 0 streams
+ * step st's operands into ring slot st % ns as soon as the consumers have released that slot
+ * (full[slot] = TMA completion, empty[slot] = one arrive by consumer thread 0 after the step's
+ * barrier).  The bulk-copy issue is off the consumers' critical path. */
 template <int NX, bool BWD>
 static __device__ __noinline__ void admm_chain(const Prob& p, const AdmmScr& sc, double* sm, const AdmmSmem& s, int nchain,
                                                int ns, ChainSeq& cs) {
   extern __shared__ __align__(16) double sm_admm[];
   sm = sm_admm;
   const int tid = threadIdx.x;
-  if (tid >= nchain) return;
   constexpr int KP = (NX + 7) / 8, SD = admm_chain_stage<NX>();
-  const int T = p.T, i = tid >> 2, q = tid & 3;
-  const bool valid = i < NX;
-  const int ic = valid ? i : 0;
-  const double* M = BWD ? sc.acl : sc.aclr;
-  double* vb = sm + s.vb;
+  const int T = p.T;
+  const double* M = sc.acl;    /* col-major: BWD walks columns (rows of Acl^T), FWD walks rows with stride NX */
   double* ring = sm + s.ws0;   /* the knot-parallel phases' per-warp area is idle during a chain */
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sm + s.cbars);
+  uint64_t* full = reinterpret_cast<uint64_t*>(sm + s.cbars);
+  uint64_t* empty = full + 8;
   auto knot_of = [&](int st) { return BWD ? T - 1 - st : st; };
-  /* one elected thread streams step st's operands into ring slot `slot`: the knot's matrix and the
-   * step's additive vectors (BWD: r_t and Vxx_fs_{t-1}; FWD: b_t, which sits in the dx~_{t+1} slot) */
-  int islot = cs.slot;
-  auto issue = [&](int st) {
-    if (tid == 0) {
-      const int t = knot_of(st);
-      double* dst = ring + (size_t)islot * SD;
-      uint64_t* bar = bars + islot;
-      const bool two = BWD && t > 0;
-      mbar_expect_tx(bar, (uint32_t)(NX * NX + NX + (two ? NX : 0)) * 8u);
-      tma_bulk_g2s(dst, M + (size_t)t * NX * NX, NX * NX * 8, bar);
-      if (BWD) {
-        tma_bulk_g2s(dst + NX * NX, sc.rv + (size_t)t * NX, NX * 8, bar);
-        if (two) tma_bulk_g2s(dst + NX * NX + NX, p.Vxx_fs + (size_t)(t - 1) * NX, NX * 8, bar);
-      } else {
-        tma_bulk_g2s(dst + NX * NX, p.dxt + (size_t)(t + 1) * NX, NX * 8, bar);
+  /* ring position after this call (every thread of the CTA keeps the same bookkeeping) */
+  const int slot0 = cs.slot;
+  const uint32_t phase0 = cs.phase;
+  {
+    const int adv = slot0 + T;
+    cs.slot = adv % ns;
+    cs.phase = phase0 ^ (uint32_t)((adv / ns) & 1);
+  }
+  if (tid >= nchain) {
+    if (tid == nchain) { /* producer */
+      int slot = slot0;
+      uint32_t ephase = phase0 ^ 1u; /* a fresh / fully drained slot: waiting on the PREVIOUS phase returns at once */
+      for (int st = 0; st < T; ++st) {
+        mbar_wait(empty + slot, ephase);
+        const int t = knot_of(st);
+        double* dst = ring + (size_t)slot * SD;
+        uint64_t* bar = full + slot;
+        const bool two = BWD && t > 0;
+        mbar_expect_tx(bar, (uint32_t)(NX * NX + NX + (two ? NX : 0)) * 8u);
+        tma_bulk_g2s(dst, M + (size_t)t * NX * NX, NX * NX * 8, bar);
+        if (BWD) {
+          tma_bulk_g2s(dst + NX * NX, sc.rv + (size_t)t * NX, NX * 8, bar);
+          if (two) tma_bulk_g2s(dst + NX * NX + NX, p.Vxx_fs + (size_t)(t - 1) * NX, NX * 8, bar);
+        } else {
+          tma_bulk_g2s(dst + NX * NX, p.dxt + (size_t)(t + 1) * NX, NX * 8, bar);
+        }
+        if (++slot == ns) { slot = 0; ephase ^= 1u; }
       }
     }
-    if (++islot == ns) islot = 0;
-  };
-  for (int st = 0; st < ns && st < T; ++st) issue(st);
+    return;
+  }
+  const int i = tid >> 2, q = tid & 3;
+  const bool valid = i < NX;
+  const int ic = valid ? i : 0;
+  double* vb = sm + s.vb;
   if (tid < NX) vb[tid] = BWD ? sc.tv[(size_t)(T - 1) * NX + tid] : p.dxt[tid];
   named_bar_sync(1, nchain);
-  int wslot = cs.slot;
-  uint32_t wphase = cs.phase;
+  int wslot = slot0;
+  uint32_t wphase = phase0;
   for (int st = 0; st < T; ++st) {
     const int t = knot_of(st);
     const double* v = vb + (st & 1) * NX;
     double* vn = vb + ((st + 1) & 1) * NX;
-    mbar_wait(bars + wslot, wphase);
+    mbar_wait(full + wslot, wphase);
     const double* stg = ring + (size_t)wslot * SD;
-    const double* row = stg + ic * NX;
     double a0 = 0.0, a1 = 0.0;
+    if (BWD) { /* (Acl^T tmp)_i: column i of Acl is contiguous */
+      const double* row = stg + ic * NX;
 #pragma unroll
-    for (int m = 0; m < KP; ++m) {
-      const int k = 2 * q + 8 * m;
-      if (k < NX) {
-        const double2 mv = *reinterpret_cast<const double2*>(row + k);
-        const double2 vv = *reinterpret_cast<const double2*>(v + k);
-        a0 = fma(mv.x, vv.x, a0);
-        a1 = fma(mv.y, vv.y, a1);
+      for (int m = 0; m < KP; ++m) {
+        const int k = 2 * q + 8 * m;
+        if (k < NX) {
+          const double2 mv = *reinterpret_cast<const double2*>(row + k);
+          const double2 vv = *reinterpret_cast<const double2*>(v + k);
+          a0 = fma(mv.x, vv.x, a0);
+          a1 = fma(mv.y, vv.y, a1);
+        }
+      }
+    } else {   /* (Acl x)_i: row i, stride NX; lane q takes columns q, q + 4, ... */
+#pragma unroll
+      for (int m = 0; m < (NX + 7) / 8; ++m) {
+        const int j0 = q + 8 * m, j1 = j0 + 4;
+        if (j0 < NX) a0 = fma(stg[ic + NX * j0], v[j0], a0);
+        if (j1 < NX) a1 = fma(stg[ic + NX * j1], v[j1], a1);
       }
     }
     double acc = a0 + a1;
     acc += __shfl_xor_sync(MG_FULLMASK, acc, 1);
     acc += __shfl_xor_sync(MG_FULLMASK, acc, 2);
+    double out0 = 0.0, out1 = 0.0;
     if (valid && q == 0) {
-      const double c0 = stg[NX * NX + i];
+      out0 = stg[NX * NX + i] + acc;                            /* Vx_t | dx~_{t+1} */
+      if (BWD && t > 0) { out1 = out0 + stg[NX * NX + NX + i]; vn[i] = out1; }   /* tmp_{t-1} */
+      if (!BWD) vn[i] = out0;
+    }
+    named_bar_sync(1, nchain);   /* step st complete: its slot is free, v_{st+1} visible */
+    if (tid == 0) mbar_arrive(empty + wslot);
+    if (valid && q == 0) {       /* the global stores are off the chain's critical path */
       if (BWD) {
-        const double vx = c0 + acc;
-        p.Vx[(size_t)t * NX + i] = vx;
-        if (t > 0) {
-          const double tn = vx + stg[NX * NX + NX + i];
-          sc.tv[(size_t)(t - 1) * NX + i] = tn;
-          vn[i] = tn;
-        }
+        p.Vx[(size_t)t * NX + i] = out0;
+        if (t > 0) sc.tv[(size_t)(t - 1) * NX + i] = out1;
       } else {
-        const double xn = c0 + acc;
-        p.dxt[(size_t)(t + 1) * NX + i] = xn;
-        vn[i] = xn;
+        p.dxt[(size_t)(t + 1) * NX + i] = out0;
       }
     }
     if (++wslot == ns) { wslot = 0; wphase ^= 1u; }
-    named_bar_sync(1, nchain);   /* step st complete: its slot is free, v_{st+1} visible */
-    if (st + ns < T) issue(st + ns);
   }
-  cs.slot = wslot;
-  cs.phase = wphase;
 }
 
 /* --------------------------------------------- gains and b_t after the backward chain */
-/* Per-warp TMA stage of the knot-parallel phases (STAGED shapes): lane 0 pulls the knot's matrix
- * blocks into the warp's shared-memory stage with bulk copies that complete on the warp's
- * mbarrier; `seq` counts the loads of this warp (phase parity), it persists across phases. */
-struct WarpStage {
-  uint64_t* bar;
-  double* buf;
-  uint32_t seq;
-  __device__ __forceinline__ void begin(uint32_t bytes, int lane) { if (lane == 0) mbar_expect_tx(bar, bytes); }
-  __device__ __forceinline__ void copy(int off, const double* src, int ndoubles, int lane) {
-    if (lane == 0 && ndoubles > 0) tma_bulk_g2s(buf + off, src, (uint32_t)ndoubles * 8u, bar);
-  }
-  __device__ __forceinline__ void wait() { mbar_wait(bar, seq & 1u); ++seq; }
+/* Per-warp software pipeline of the knot-parallel phases (STAGED shapes).  A warp walks its knots
+ * t, t + nw, ...; while it works on knot t
+ *   - the knot's FIRST block (K in the update phase, Fu in the gains phase: used first and last) sits
+ *     in one of two shared-memory buffers, the next knot's copy streams into the other (TMA bulk copy
+ *     issued by lane 0 at the top of the knot, completing on the buffer's mbarrier);
+ *   - the SECOND block ([Gx Gu] / LLT) has one buffer, refilled for the next knot right after its
+ *     last use in this knot;
+ *   - the next knot's vectors are already on their way into registers.
+ * So no step of a knot waits for global memory once the pipeline runs.  `WSeq` counts the loads
+ * of this warp per buffer family (mbarrier phase parity); it persists across phases. */
+struct WSeq {
+  uint32_t a, b;
 };
+struct WarpPipe {
+  uint64_t* abar; /* [2] */
+  uint64_t* bbar; /* [1] */
+  double* abuf;   /* 2 x asz */
+  double* bbuf;
+  int asz;
+  uint32_t ia, wa, ib, wb; /* issue / wait counters */
+  __device__ __forceinline__ void issue_a(const double* src, int ndoubles, int lane) {
+    if (lane == 0) {
+      uint64_t* bar = abar + (ia & 1u);
+      mbar_expect_tx(bar, (uint32_t)ndoubles * 8u);
+      tma_bulk_g2s(abuf + (ia & 1u) * asz, src, (uint32_t)ndoubles * 8u, bar);
+    }
+    ++ia;
+  }
+  __device__ __forceinline__ const double* wait_a() {
+    mbar_wait(abar + (wa & 1u), (wa >> 1) & 1u);
+    const double* r = abuf + (wa & 1u) * asz;
+    ++wa;
+    return r;
+  }
+  /* two source blocks land back to back in the single B buffer */
+  __device__ __forceinline__ void issue_b(const double* s0, int n0, const double* s1, int n1, int lane) {
+    if (lane == 0) {
+      mbar_expect_tx(bbar, (uint32_t)(n0 + n1) * 8u);
+      tma_bulk_g2s(bbuf, s0, (uint32_t)n0 * 8u, bbar);
+      if (n1 > 0) tma_bulk_g2s(bbuf + n0, s1, (uint32_t)n1 * 8u, bbar);
+    }
+    ++ib;
+  }
+  __device__ __forceinline__ void wait_b() { mbar_wait(bbar, wb & 1u); ++wb; }
+};
+template <int NX, int NU>
+__device__ __forceinline__ WarpPipe warp_pipe(double* sm, const AdmmSmem& s, int warp, const WSeq& q) {
+  WarpPipe w;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sm + s.wbars) + 3 * warp;
+  double* ws = sm + s.ws0 + warp * s.wsn;
+  w.abar = bars; w.bbar = bars + 2;
+  w.abuf = ws + s.stg; w.asz = NX * NU; w.bbuf = w.abuf + 2 * NX * NU;
+  w.ia = w.wa = q.a; w.ib = w.wb = q.b;
+  return w;
+}
 
 /* Qu_t = qu_t + Fu_t^T tmp_t, k_t = Quu_t^-1 Qu_t (src/csqp.cpp:1083-1097), b_t = fs_{t+1} - Fu_t k_t;
  * one warp per knot.  qu_t was left in the Qu_ slot by admm_update. */
 template <int NX, int NU, bool STAGED>
 static __device__ __noinline__ void admm_gains(const Prob& p, const AdmmScr& sc, double* sm, const AdmmSmem& s,
-                                               uint32_t& wseq) {
+                                               WSeq& wseq) {
   extern __shared__ __align__(16) double sm_admm[];
   sm = sm_admm;
   using W = AdmmWs<NX, NU>;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  const int T = p.T;
   double* ws = sm + s.ws0 + warp * s.wsn;
   double *xs = ws + W::xs, *us = ws + W::us, *qu = ws + W::qu;
-  WarpStage stg{reinterpret_cast<uint64_t*>(sm + s.wbars) + warp, ws + s.stg, wseq};
+  WarpPipe wp = warp_pipe<NX, NU>(sm, s, warp, wseq);
   auto pull = [&](int t) { /* knot t's blocks and vectors -> L2 */
-    if (t >= p.T) return;
+    if (t >= T) return;
     pf_block(p.Fu + (size_t)t * NX * NU, NX * NU, lane);
     pf_block(p.L + (size_t)t * NU * NU, NU * NU, lane - 1);
     pf_vec(sc.tv + (size_t)t * NX, NX, lane - 2);
     pf_vec(p.fs + (size_t)(t + 1) * NX, NX, lane - 10);
     pf_vec(p.Qu + (size_t)t * NU, NU, lane - 18);
   };
-  pull(warp + nw);
-  for (int t = warp; t < p.T; t += nw) {
-    const double* Fu = p.Fu + (size_t)t * NX * NU;
-    const double* L = p.L + (size_t)t * NU * NU;
+  double ntv0 = 0.0, ntv1 = 0.0, nfs0 = 0.0, nfs1 = 0.0, nqu = 0.0;
+  auto fetch = [&](int t) { /* knot t's vectors into registers */
+    if (t >= T) return;
+    if (lane < NX) { ntv0 = sc.tv[(size_t)t * NX + lane]; nfs0 = p.fs[(size_t)(t + 1) * NX + lane]; }
+    if (NX > 32 && lane + 32 < NX) { ntv1 = sc.tv[(size_t)t * NX + lane + 32]; nfs1 = p.fs[(size_t)(t + 1) * NX + lane + 32]; }
+    if (lane < NU) nqu = p.Qu[(size_t)t * NU + lane];
+  };
+  if (warp < T) {
     if constexpr (STAGED) {
-      stg.begin((uint32_t)(NX * NU + NU * NU) * 8u, lane);
-      stg.copy(0, Fu, NX * NU, lane);
-      stg.copy(NX * NU, L, NU * NU, lane);
+      wp.issue_a(p.Fu + (size_t)warp * NX * NU, NX * NU, lane);
+      wp.issue_b(p.L + (size_t)warp * NU * NU, NU * NU, nullptr, 0, lane);
     }
-    pull(t + 2 * nw);
-    /* the knot's vectors: all loads in flight at once */
-    double tv0 = 0.0, tv1 = 0.0, fs0 = 0.0, fs1 = 0.0, quv = 0.0;
-    if (lane < NX) { tv0 = sc.tv[(size_t)t * NX + lane]; fs0 = p.fs[(size_t)(t + 1) * NX + lane]; }
-    if (NX > 32 && lane + 32 < NX) { tv1 = sc.tv[(size_t)t * NX + lane + 32]; fs1 = p.fs[(size_t)(t + 1) * NX + lane + 32]; }
-    if (lane < NU) quv = p.Qu[(size_t)t * NU + lane];
-    if (lane < NX) xs[lane] = tv0;
-    if (NX > 32 && lane + 32 < NX) xs[lane + 32] = tv1;
+    fetch(warp);
+  }
+  pull(warp + nw);
+  for (int t = warp; t < T; t += nw) {
+    const int tn = t + nw;
+    const double fs0 = nfs0, fs1 = nfs1;
+    if (lane < NX) xs[lane] = ntv0;
+    if (NX > 32 && lane + 32 < NX) xs[lane + 32] = ntv1;
     if (NX > 64) for (int i = lane + 64; i < NX; i += 32) xs[i] = sc.tv[(size_t)t * NX + i];
-    if (lane < NU) qu[lane] = quv;
-    if constexpr (STAGED) stg.wait();
+    if (lane < NU) qu[lane] = nqu;
+    if constexpr (STAGED) { if (tn < T) wp.issue_a(p.Fu + (size_t)tn * NX * NU, NX * NU, lane); }
+    pull(t + 2 * nw);
+    fetch(tn);
+    const double* mFu = p.Fu + (size_t)t * NX * NU;
+    const double* mL = p.L + (size_t)t * NU * NU;
+    if constexpr (STAGED) mFu = wp.wait_a();
     __syncwarp();
-    auto body = [&](const double* mFu, const double* mL) {
-      wdot4<NX>(mFu, NU, xs, lane, [&](int a, double acc) {
-        double v = qu[a];
-        v += acc;
-        us[a] = v;                      /* Qu_t (us doubles as its buffer until the solve) */
-        p.Qu[(size_t)t * NU + a] = v;
-      });
-      __syncwarp();
-      double ki = (lane < NU) ? us[lane] : 0.0;
-      ki = wsolve_llt<NU>(mL, ki, lane);
-      __syncwarp();
-      if (lane < NU) { us[lane] = ki; p.kff[(size_t)t * NU + lane] = ki; }
-      __syncwarp();
-      waxpy<NX, NU>(mFu, us, lane, [&](int i, double acc) {
-        /* the lane that owns row i also loaded fs_{t+1}[i] */
-        const double f = (i < 32) ? fs0 : (i < 64) ? fs1 : p.fs[(size_t)(t + 1) * NX + i];
-        p.dxt[(size_t)(t + 1) * NX + i] = f - acc;
-      });
-    };
-    if constexpr (STAGED) body(stg.buf, stg.buf + NX * NU);
-    else body(Fu, L);
+    wdot4<NX>(mFu, NU, xs, lane, [&](int a, double acc) {
+      double v = qu[a];
+      v += acc;
+      us[a] = v;                      /* Qu_t (us doubles as its buffer until the solve) */
+      p.Qu[(size_t)t * NU + a] = v;
+    });
+    __syncwarp();
+    double ki = (lane < NU) ? us[lane] : 0.0;
+    if constexpr (STAGED) { wp.wait_b(); mL = wp.bbuf; }
+    ki = wsolve_llt<NU>(mL, ki, lane);
+    __syncwarp();
+    if constexpr (STAGED) { if (tn < T) wp.issue_b(p.L + (size_t)tn * NU * NU, NU * NU, nullptr, 0, lane); }
+    if (lane < NU) { us[lane] = ki; p.kff[(size_t)t * NU + lane] = ki; }
+    __syncwarp();
+    waxpy<NX, NU>(mFu, us, lane, [&](int i, double acc) {
+      /* the lane that owns row i also loaded fs_{t+1}[i] */
+      const double f = (i < 32) ? fs0 : (i < 64) ? fs1 : p.fs[(size_t)(t + 1) * NX + i];
+      p.dxt[(size_t)(t + 1) * NX + i] = f - acc;
+    });
     __syncwarp();
   }
-  wseq = stg.seq;
+  wseq.a = wp.wa; wseq.b = wp.wb;
   fence_proxy_async(); /* b_t -> the forward chain's TMA */
 }
 
@@ -481,7 +544,7 @@ static __device__ __noinline__ void admm_gains(const Prob& p, const AdmmScr& sc,
 template <int NX, int NU, bool STAGED>
 static __device__ __noinline__ void admm_update(const Prob& p, const AdmmScr& sc, double* sm, const AdmmSmem& s,
                                                 const mimgpu_csqp_params& q_, int iter, bool need_r, bool stage_g,
-                                                AdmmNorms& n, uint32_t& wseq) {
+                                                AdmmNorms& n, WSeq& wseq) {
   extern __shared__ __align__(16) double sm_admm[];
   sm = sm_admm;
   using W = AdmmWs<NX, NU>;
@@ -491,12 +554,13 @@ static __device__ __noinline__ void admm_update(const Prob& p, const AdmmScr& sc
   double* ws = sm + s.ws0 + warp * s.wsn;
   double *xs = ws + W::xs, *us = ws + W::us, *sqx = ws + W::qx, *squ = ws + W::qu, *sd = ws + W::ds, *se1 = sd + ngm,
          *se2 = se1 + ngm;
-  WarpStage stg{reinterpret_cast<uint64_t*>(sm + s.wbars) + warp, ws + s.stg, wseq};
+  WarpPipe wp = warp_pipe<NX, NU>(sm, s, warp, wseq);
   const bool check = (iter % q_.rho_update_interval) == 0;
   const bool heur = q_.update_rho_with_heuristic != 0;
   const bool dualg = check && !heur;
   const double alpha = q_.alpha, sigma = q_.sigma;
   double np_ = -CUDART_INF, nd_ = -CUDART_INF, npr = -CUDART_INF, ndr = -CUDART_INF; /* src/csqp.cpp:1201-1204 */
+  const bool sg = STAGED && stage_g && ng > 0; /* [Gx Gu] of the running knots go through the B buffer */
 
   /* row r of one knot: c given, z / y projection and the row-local norms (src/csqp.cpp:1231-1239) */
   auto project = [&](size_t o, int r, double c, double zp, double rho, double yo, double lo, double hi) {
@@ -537,63 +601,65 @@ static __device__ __noinline__ void admm_update(const Prob& p, const AdmmScr& sc
     pf_vec(p.kff + (size_t)t * NU, NU, lane - 19);
     if (need_r) { pf_vec(p.Lx + (size_t)t * NX, NX, lane - 11); pf_vec(p.Lu + (size_t)t * NU, NU, lane - 19); }
   };
-  pull(warp + nw);
-  for (int t = warp; t <= T; t += nw) {
+  /* vectors of the NEXT knot, in registers */
+  double nx0 = 0.0, nx1 = 0.0, nkf = 0.0, nlx0 = 0.0, nlx1 = 0.0, nlu = 0.0;
+  double nzp = 0.0, nrho = 1.0, nyo = 0.0, nlo = 0.0, nhi = 0.0;
+  auto fetch = [&](int t) {
+    if (t > T) return;
     const bool last = (t == T);
     const int nc = last ? ngT : ng;
     const size_t o = (size_t)t * ng;
-    const double* Kg = p.K + (size_t)(last ? 0 : t) * NX * NU;
-    const double* Gxg = last ? p.GxT : (ng ? p.Gx + (size_t)t * ng * NX : nullptr);
-    const double* Gug = (last || !ng) ? nullptr : p.Gu + (size_t)t * ng * NU;
-    const bool sg = STAGED && stage_g && !last && ng > 0;
-    if constexpr (STAGED) {
-      if (!last) {
-        stg.begin((uint32_t)(NX * NU + (sg ? ng * (NX + NU) : 0)) * 8u, lane);
-        stg.copy(0, Kg, NX * NU, lane);
-        if (sg) { stg.copy(NX * NU, Gxg, ng * NX, lane); stg.copy(NX * NU + ng * NX, Gug, ng * NU, lane); }
-      }
-    }
-    pull(t + 2 * nw);
-    /* the knot's vectors: every load in flight before the first use */
-    double x0 = 0.0, x1 = 0.0, kf = 0.0, lx0 = 0.0, lx1 = 0.0, luv = 0.0;
-    double zp = 0.0, rho = 1.0, yo = 0.0, lo = 0.0, hi = 0.0;
-    const bool rowreg = nc > 0 && nc <= 32;   /* lane r holds row r's vectors */
-    if (lane < NX) x0 = p.dxt[(size_t)t * NX + lane];
-    if (NX > 32 && lane + 32 < NX) x1 = p.dxt[(size_t)t * NX + lane + 32];
-    if (!last && lane < NU) kf = p.kff[(size_t)t * NU + lane];
-    if (rowreg && lane < nc) {
+    if (lane < NX) nx0 = p.dxt[(size_t)t * NX + lane];
+    if (NX > 32 && lane + 32 < NX) nx1 = p.dxt[(size_t)t * NX + lane + 32];
+    if (!last && lane < NU) nkf = p.kff[(size_t)t * NU + lane];
+    if (nc > 0 && nc <= 32 && lane < nc) { /* lane r holds row r's vectors */
       const double* g = last ? p.gT : p.g + o;
       const double* lb = last ? p.glbT : p.glb + o;
       const double* ub = last ? p.gubT : p.gub + o;
-      zp = p.z[o + lane]; rho = p.rho[o + lane]; yo = p.y[o + lane];
+      nzp = p.z[o + lane]; nrho = p.rho[o + lane]; nyo = p.y[o + lane];
       const double gv = g[lane];
-      lo = lb[lane] - gv; hi = ub[lane] - gv;
+      nlo = lb[lane] - gv; nhi = ub[lane] - gv;
     }
     if (need_r && !last) {
-      if (lane < NX) lx0 = p.Lx[(size_t)t * NX + lane];
-      if (NX > 32 && lane + 32 < NX) lx1 = p.Lx[(size_t)t * NX + lane + 32];
-      if (lane < NU) luv = p.Lu[(size_t)t * NU + lane];
+      if (lane < NX) nlx0 = p.Lx[(size_t)t * NX + lane];
+      if (NX > 32 && lane + 32 < NX) nlx1 = p.Lx[(size_t)t * NX + lane + 32];
+      if (lane < NU) nlu = p.Lu[(size_t)t * NU + lane];
     }
-    if (lane < NX) { xs[lane] = x0; p.dx[(size_t)t * NX + lane] = x0; }
-    if (NX > 32 && lane + 32 < NX) { xs[lane + 32] = x1; p.dx[(size_t)t * NX + lane + 32] = x1; }
+  };
+  auto issue_k = [&](int t) { if (STAGED && t < T) wp.issue_a(p.K + (size_t)t * NX * NU, NX * NU, lane); };
+  auto issue_g = [&](int t) {
+    if (sg && t < T) wp.issue_b(p.Gx + (size_t)t * ng * NX, ng * NX, p.Gu + (size_t)t * ng * NU, ng * NU, lane);
+  };
+  issue_k(warp);
+  issue_g(warp);
+  fetch(warp);
+  pull(warp + nw);
+  for (int t = warp; t <= T; t += nw) {
+    const bool last = (t == T);
+    const int nc = last ? ngT : ng, tn = t + nw;
+    const size_t o = (size_t)t * ng;
+    const bool rowreg = nc > 0 && nc <= 32;
+    /* ---- commit the prefetched vectors; start the next knot's loads */
+    const double zp = nzp, rho = nrho, yo = nyo, lo = nlo, hi = nhi;
+    if (lane < NX) { xs[lane] = nx0; p.dx[(size_t)t * NX + lane] = nx0; }
+    if (NX > 32 && lane + 32 < NX) { xs[lane + 32] = nx1; p.dx[(size_t)t * NX + lane + 32] = nx1; }
     if (NX > 64)
       for (int i = lane + 64; i < NX; i += 32) { const double x = p.dxt[(size_t)t * NX + i]; xs[i] = x; p.dx[(size_t)t * NX + i] = x; }
-    if (need_r && !last) { /* qx_t / qu_t start from Lx - sigma dx~ and Lu (the G^T d and -sigma du~ terms follow) */
-      if (lane < NX) sqx[lane] = lx0;
-      if (NX > 32 && lane + 32 < NX) sqx[lane + 32] = lx1;
+    if (need_r && !last) { /* qx_t / qu_t start from Lx and Lu (the -sigma and G^T d terms follow) */
+      if (lane < NX) sqx[lane] = nlx0;
+      if (NX > 32 && lane + 32 < NX) sqx[lane + 32] = nlx1;
       if (NX > 64) for (int i = lane + 64; i < NX; i += 32) sqx[i] = p.Lx[(size_t)t * NX + i];
-      if (lane < NU) squ[lane] = luv;
+      if (lane < NU) squ[lane] = nlu;
     }
-    if (!last && lane < NU) us[lane] = kf;    /* k_t, replaced by du~_t below */
-    if constexpr (STAGED) { if (!last) stg.wait(); }
+    if (!last && lane < NU) us[lane] = nkf;    /* k_t, replaced by du~_t below */
+    issue_k(tn);
+    pull(t + 2 * nw);
+    fetch(tn);
+    const double* K = p.K + (size_t)(last ? 0 : t) * NX * NU;
+    const double* Gx = last ? p.GxT : (ng ? p.Gx + (size_t)t * ng * NX : nullptr);
+    const double* Gu = (last || !ng) ? nullptr : p.Gu + (size_t)t * ng * NU;
+    if constexpr (STAGED) { if (!last) K = wp.wait_a(); }
     __syncwarp();
-    const double* K = Kg;
-    const double* Gx = Gxg;
-    const double* Gu = Gug;
-    if constexpr (STAGED) {
-      if (!last) K = stg.buf;
-      if (sg) { Gx = stg.buf + NX * NU; Gu = Gx + ng * NX; }
-    }
     if (!last) { /* du~ = -k - K dx~ (src/csqp.cpp:636-637); us[a] holds k_t[a] and is replaced by du~_t[a] */
       wdot4<NX>(K, NU, xs, lane, [&](int a, double acc) {
         double u = -us[a];
@@ -604,6 +670,7 @@ static __device__ __noinline__ void admm_update(const Prob& p, const AdmmScr& sc
       });
       __syncwarp();
     }
+    if (sg && !last) { wp.wait_b(); Gx = wp.bbuf; Gu = Gx + ng * NX; }
     if (nc) {
       /* c_r = sum_j Gx[r][j] dx~[j] + sum_a Gu[r][a] du~[a]: lanes over rows, columns split over lane groups */
       const int np2 = nc <= 4 ? 4 : nc <= 8 ? 8 : nc <= 16 ? 16 : 32, ph_n = 32 / np2;
@@ -701,14 +768,15 @@ static __device__ __noinline__ void admm_update(const Prob& p, const AdmmScr& sc
           p.Qu[(size_t)t * NU + a] = v;
         }
       }
-      __syncwarp();
-      if (need_r) { /* r_t = qx_t - K_t^T qu_t; K row-major NU x NX = col-major NX x NU */
-        waxpy<NX, NU>(K, squ, lane, [&](int i, double acc) { sc.rv[(size_t)t * NX + i] = sqx[i] - acc; });
-      }
+    }
+    __syncwarp();
+    issue_g(tn);   /* the G buffer is free: every lane is past its last read */
+    if (need_r) { /* r_t = qx_t - K_t^T qu_t; K row-major NU x NX = col-major NX x NU */
+      waxpy<NX, NU>(K, squ, lane, [&](int i, double acc) { sc.rv[(size_t)t * NX + i] = sqx[i] - acc; });
     }
     __syncwarp();
   }
-  wseq = stg.seq;
+  wseq.a = wp.wa; wseq.b = wp.wb;
   fence_proxy_async(); /* r_t -> the backward chain's TMA */
   /* src/csqp.cpp:1201-1204: the four norms are -inf unless this is a check iteration */
   n.primal = n.dual = n.primal_rel = n.dual_rel = -CUDART_INF;
@@ -730,7 +798,8 @@ static __device__ __noinline__ void admm_update(const Prob& p, const AdmmScr& sc
 struct AdmmKPar {
   mimgpu_csqp_params q;
   int with_kkt, ric_total, nchain, stage_g, chain_ns;
-  double *acl, *aclr, *rv, *tv; /* [B][T][...] scratch of the condensed iterations */
+  double *acl, *rv, *tv; /* [B][T][...] scratch of the condensed iterations */
+  long long* timing;            /* debug (MIMGPU_ADMM_TIMING): clock64 cycles of CTA 0 per phase, or null */
 };
 
 /* shapes whose knot blocks go through a per-warp TMA stage in the knot-parallel phases (the
@@ -738,13 +807,21 @@ struct AdmmKPar {
 template <int NX, int NU>
 __host__ __device__ constexpr bool admm_staged() { return NX <= 36; }
 
-template <int NX, int NU> struct AdmmTune { static constexpr int MAXT = NX <= 16 ? 128 : 256, MINB = NX <= 16 ? 6 : 2; };
-template <> struct AdmmTune<36, 12> { static constexpr int MAXT = 192, MINB = 2; };
-template <> struct AdmmTune<12, 6> { static constexpr int MAXT = 96, MINB = 8; };
-template <> struct AdmmTune<32, 16> { static constexpr int MAXT = 192, MINB = 2; };
-template <> struct AdmmTune<64, 32> { static constexpr int MAXT = 384, MINB = 1; };
-template <> struct AdmmTune<76, 32> { static constexpr int MAXT = 384, MINB = 1; };
-template <> struct AdmmTune<48, 24> { static constexpr int MAXT = 256, MINB = 1; };
+/* MAXT: CTA size; MINB: resident CTAs per SM the register allocation aims at; RBUF: F / G buffers of
+ * the DMMA Riccati sweep (2 = next knot streams in while this one is processed, 1 = smaller CTA) */
+#ifndef MIMGPU_ADMM_C3_MINB
+#define MIMGPU_ADMM_C3_MINB 2
+#endif
+#ifndef MIMGPU_ADMM_C3_RBUF
+#define MIMGPU_ADMM_C3_RBUF 2
+#endif
+template <int NX, int NU> struct AdmmTune { static constexpr int MAXT = NX <= 16 ? 128 : 256, MINB = NX <= 16 ? 6 : 2, RBUF = 2; };
+template <> struct AdmmTune<36, 12> { static constexpr int MAXT = 192, MINB = MIMGPU_ADMM_C3_MINB, RBUF = MIMGPU_ADMM_C3_RBUF; };
+template <> struct AdmmTune<12, 6> { static constexpr int MAXT = 96, MINB = 8, RBUF = 2; };
+template <> struct AdmmTune<32, 16> { static constexpr int MAXT = 192, MINB = 2, RBUF = 2; };
+template <> struct AdmmTune<64, 32> { static constexpr int MAXT = 384, MINB = 1, RBUF = 2; };
+template <> struct AdmmTune<76, 32> { static constexpr int MAXT = 384, MINB = 1, RBUF = 2; };
+template <> struct AdmmTune<48, 24> { static constexpr int MAXT = 256, MINB = 1, RBUF = 2; };
 
 template <int MODE>
 static __device__ __noinline__ int admm_riccati_generic(const Prob& p, double* sm, const Smem& s, const RicPar& rp,
@@ -772,23 +849,23 @@ k_csqp_direction_admm(KArgs a, AdmmKPar kp) {
   double* gsm = sm + ss.uni; /* Riccati layouts live in the union region */
   const Smem gs = smem_layout(NX, NU, p.ng, p.ngT, a.stage_fx);
   RicSmem rs{};
-  if constexpr (USE_MMA) rs = ric_layout<NX, NU>(p.ng, p.ngT, true);
+  if constexpr (USE_MMA) rs = ric_layout<NX, NU>(p.ng, p.ngT, true, AdmmTune<NX, NU>::RBUF);
   uint64_t* ric_bars = reinterpret_cast<uint64_t*>(sm + ss.bars);
   uint32_t ric_seq = 0u;
   if (threadIdx.x == 0) {
     mbar_init(ric_bars, 1);
     mbar_init(ric_bars + 1, 1);
-    for (int w = 0; w < nw; ++w) mbar_init(reinterpret_cast<uint64_t*>(sm + ss.wbars) + w, 1);
-    for (int w = 0; w < 8; ++w) mbar_init(reinterpret_cast<uint64_t*>(sm + ss.cbars) + w, 1);
+    for (int w = 0; w < 3 * nw; ++w) mbar_init(reinterpret_cast<uint64_t*>(sm + ss.wbars) + w, 1);
+    for (int w = 0; w < 16; ++w) mbar_init(reinterpret_cast<uint64_t*>(sm + ss.cbars) + w, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
-  uint32_t wseq = 0u; /* loads this warp has put through its TMA stage */
+  WSeq wseq{0u, 0u};  /* loads this warp has put through its pipeline buffers */
   ChainSeq cseq{0, 0u};  /* ring position of the chains' TMA pipeline */
   AdmmScr sc;
   {
     const size_t sb = (size_t)b * p.T;
-    sc.acl = kp.acl + sb * NX * NX; sc.aclr = kp.aclr + sb * NX * NX;
+    sc.acl = kp.acl + sb * NX * NX;
     sc.rv = kp.rv + sb * NX; sc.tv = kp.tv + sb * NX;
   }
   const mimgpu_csqp_params& q = kp.q;
@@ -815,6 +892,12 @@ k_csqp_direction_admm(KArgs a, AdmmKPar kp) {
   }
   const int interval = q.rho_update_interval;
   auto is_full = [&](int k) { return k % interval == 1 || interval == 1; };
+  long long tk0 = 0;
+  const bool timed = kp.timing != nullptr && blockIdx.x == 0 && threadIdx.x == 0;
+  auto tick = [&](int slot) { /* phase timer of CTA 0 (debug switch; one predicated branch per phase otherwise) */
+    if (timed) { const long long c = clock64(); kp.timing[slot] += c - tk0; tk0 = c; }
+  };
+  if (timed) tk0 = clock64();
   if (!st) {
     for (it = 1; it < q.max_qp_iters + 1; ++it) { /* src/csqp.cpp:470 */
       if (is_full(it)) {
@@ -822,17 +905,24 @@ k_csqp_direction_admm(KArgs a, AdmmKPar kp) {
         else st = admm_riccati_generic<MODE_FULL>(p, gsm, gs, rp, a.stage_fx);
         if (st) break;
         __syncthreads();
+        tick(0);
         admm_post_full<NX, NU>(p, sc, sm, ss);
+        __syncthreads();
+        tick(1);
       } else {
         admm_chain<NX, true>(p, sc, sm, ss, kp.nchain, kp.chain_ns, cseq);
         __syncthreads();
+        tick(2);
         admm_gains<NX, NU, STAGED>(p, sc, sm, ss, wseq);
+        __syncthreads();
+        tick(3);
       }
-      __syncthreads();
       admm_chain<NX, false>(p, sc, sm, ss, kp.nchain, kp.chain_ns, cseq);
       __syncthreads();
+      tick(4);
       const bool need_r = (it + 1 < q.max_qp_iters + 1) && !is_full(it + 1);
       admm_update<NX, NU, STAGED>(p, sc, sm, ss, q, it, need_r, kp.stage_g != 0, n, wseq);
+      tick(5);
       if (it % interval == 0) {
         /* update_rho_vec (src/csqp.cpp:519-532) */
         const double scale = sqrt((n.primal * n.dual_rel) / (n.dual * n.primal_rel));
@@ -875,12 +965,12 @@ static AdmmPlan admm_plan_t(const mimgpu_shape& sh, int stage_fx, int max_smem) 
   const Smem gs = smem_layout(NX, NU, sh.ng, sh.ngT, stage_fx);
   pl.nt = AdmmTune<NX, NU>::MAXT;
   pl.nchain = ((4 * NX + 31) / 32) * 32;
-  if (pl.nchain > pl.nt) return pl;
+  if (pl.nchain + 32 > pl.nt) return pl; /* compute warps + one producer warp */
   for (int mma = MMA ? 1 : 0; mma >= 0; --mma) {
     int ric_total = gs.total;
     if (mma) {
       if constexpr (MMA) {
-        const RicSmem rs = ric_layout<NX, NU>(sh.ng, sh.ngT, true);
+        const RicSmem rs = ric_layout<NX, NU>(sh.ng, sh.ngT, true, AdmmTune<NX, NU>::RBUF);
         if (rs.total > ric_total) ric_total = rs.total;
       }
     }
@@ -930,10 +1020,11 @@ static inline AdmmPlan admm_plan(const mimgpu_shape& sh, int stage_fx, int max_s
 }
 
 static inline int admm_csqp_launch(const KArgs& a, const mimgpu_csqp_params& q, int with_kkt, const AdmmPlan& pl,
-                                   double* const scratch[4], cudaStream_t st) {
+                                   double* const scratch[3], cudaStream_t st, long long* timing = nullptr) {
   AdmmKPar kp;
+  kp.timing = timing;
   kp.q = q; kp.with_kkt = with_kkt; kp.ric_total = pl.ric_total; kp.nchain = pl.nchain; kp.stage_g = pl.stage_g; kp.chain_ns = pl.chain_ns;
-  kp.acl = scratch[0]; kp.aclr = scratch[1]; kp.rv = scratch[2]; kp.tv = scratch[3];
+  kp.acl = scratch[0]; kp.rv = scratch[1]; kp.tv = scratch[2];
 #define X(NX_, NU_)                                                                                         \
   if (a.sh.nx == NX_ && a.sh.nu == NU_) {                                                                   \
     if (pl.use_mma) k_csqp_direction_admm<NX_, NU_, true><<<a.n_active, pl.nt, pl.smem_bytes, st>>>(a, kp); \

@@ -36,10 +36,10 @@ int small_record_offsets_x(const mimgpu_shape& s, int out[16]);
 StreamPlan stream_plan_x(const mimgpu_shape& sh, int stage_fx, int max_smem);
 int stream_csqp_launch_x(const KArgs& a, const mimgpu_csqp_params& q, int with_kkt, const StreamPlan& pl,
                          cudaStream_t st);
-/* condensed-chain CSQP kernel (kernels_admm.cuh); scratch = {Acl, Acl row-major, r, tmp} */
+/* condensed-chain CSQP kernel (kernels_admm.cuh); scratch = {Acl, r, tmp} */
 AdmmPlan admm_plan_x(const mimgpu_shape& sh, int stage_fx, int max_smem);
 int admm_csqp_launch_x(const KArgs& a, const mimgpu_csqp_params& q, int with_kkt, const AdmmPlan& pl,
-                       double* const scratch[4], cudaStream_t st);
+                       double* const scratch[3], cudaStream_t st, long long* timing = nullptr);
 /* CTA-per-problem DMMA SQP / FDDP kernel (kernels_ric.cuh, kernels_cta.cuh) */
 CtaPlan cta_plan_x(const mimgpu_shape& sh, int stage_fx, int max_smem);
 int cta_sqp_launch_x(const KArgs& a, const SqpKPar& kp, bool fddp, const CtaPlan& pl, cudaStream_t st);

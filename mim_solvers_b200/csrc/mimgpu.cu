@@ -62,12 +62,14 @@ struct mimgpu_ctx {
   CtaPlan cplan{};                 /* DMMA CTA-per-problem SQP / FDDP kernel (kernels_cta.cuh) */
   StreamPlan splan{};              /* streaming CSQP kernel (kernels_stream.cuh), ok = 0: not available */
   AdmmPlan aplan{};                /* condensed-chain CSQP kernel (kernels_admm.cuh): the default CSQP path */
-  double* admm_scr[4] = {nullptr, nullptr, nullptr, nullptr}; /* Acl, Acl row-major, r, tmp: allocated at the first CSQP call */
+  double* admm_scr[3] = {nullptr, nullptr, nullptr}; /* Acl, r, tmp of the condensed ADMM iterations: allocated at the first CSQP call */
   /* debug / A-B switches, read ONCE at mimgpu_create (never on the hot path) */
   bool force_generic = false;      /* MIMGPU_FORCE_GENERIC: shape-generic kernels only */
-  bool csqp_stream = false;        /* MIMGPU_CSQP_STREAM: round-1 streaming CSQP kernel instead of the condensed one */
+  bool csqp_stream = false;        /* MIMGPU_CSQP_STREAM: sweep-by-sweep streaming CSQP kernel for every shape */
+  bool csqp_admm = false;          /* MIMGPU_CSQP_ADMM: condensed-chain CSQP kernel for every shape it is compiled for */
   bool small_alt = false;          /* MIMGPU_SMALL_FULL / MIMGPU_SMALL_NOMMA: full-spill small kernel as default */
   bool warned_generic = false;
+  long long* admm_timing = nullptr; /* MIMGPU_ADMM_TIMING: device counters of the per-phase debug timer */
   int last_kind = 0;               /* 0 none, 1 SQP, 2 FDDP, 3 CSQP: what the last direction call was */
   bool pack_dirty = false;         /* field-major inputs changed since the knot records were built */
   bool attached = false;           /* inputs are caller-owned device memory: re-read at EVERY direction call */
@@ -249,7 +251,9 @@ static int configure_launch(mimgpu_ctx* c) {
   c->cplan = cta_plan_x(s, stage, max_smem);
   c->force_generic = getenv("MIMGPU_FORCE_GENERIC") != nullptr;
   c->csqp_stream = getenv("MIMGPU_CSQP_STREAM") != nullptr;
+  c->csqp_admm = getenv("MIMGPU_CSQP_ADMM") != nullptr;
   c->small_alt = getenv("MIMGPU_SMALL_FULL") != nullptr || getenv("MIMGPU_SMALL_NOMMA") != nullptr;
+  if (getenv("MIMGPU_ADMM_TIMING") != nullptr) CU(cudaMalloc(&c->admm_timing, 8 * sizeof(long long)));
   return MIMGPU_OK;
 }
 
@@ -325,8 +329,8 @@ void mimgpu_destroy(mimgpu_ctx* c) {
   cudaSetDevice(c->device);
   if (c->pipe_st[0]) cudaStreamDestroy(c->pipe_st[0]);
   if (c->pipe_st[1]) cudaStreamDestroy(c->pipe_st[1]);
-  for (int i = 0; i < 4; ++i) cudaFree(c->admm_scr[i]);
-  cudaFree(c->cost_buf);
+  for (int i = 0; i < 3; ++i) cudaFree(c->admm_scr[i]);
+  cudaFree(c->cost_buf); cudaFree(c->admm_timing);
   cudaFree(c->pack_buf); cudaFree(c->spill_buf); cudaFree(c->in_buf); cudaFree(c->state_buf); cudaFree(c->ibuf); cudaFree(c->reg_buf); cudaFree(c->summary_dev);
   delete c;
 }
@@ -763,14 +767,30 @@ int mimgpu_csqp_direction(mimgpu_ctx* c, const mimgpu_csqp_params* p, int with_k
   c->spill_packed = false;
   /* 16-byte rows / TMA bulk copies need 16-byte aligned sources (block sizes are even by construction) */
   const uintptr_t al = (uintptr_t)c->k.Fx | (uintptr_t)c->k.Fu | (uintptr_t)c->k.Gx | (uintptr_t)c->k.Gu;
-  if (c->aplan.ok && !c->force_generic && !c->csqp_stream && (al & 15) == 0) {
+  /* Measured on B200 (profiles/sweep_r02_*.jsonl): the condensed-chain kernel wins from nx = 36 up (Solo12,
+   * 48/24, 64/32, Talos); below that a knot is too little work for a warp-per-knot phase and the
+   * sweep-by-sweep streaming kernel stays ahead (UR5: 108 k vs 87 k QP/s, 32/16: 11.3 k vs 10.8 k). */
+  const bool want_admm = c->csqp_admm || (c->sh.nx >= 36 && !c->csqp_stream) || !c->splan.ok;
+  if (c->aplan.ok && !c->force_generic && want_admm && (al & 15) == 0) {
     if (!c->admm_scr[0]) {
       const size_t BT = (size_t)c->sh.B * c->sh.T, nx = c->sh.nx;
-      const size_t bytes[4] = {BT * nx * nx * 8, BT * nx * nx * 8, BT * nx * 8, BT * nx * 8};
-      for (int i = 0; i < 4; ++i) CU(cudaMalloc(&c->admm_scr[i], bytes[i]));
+      const size_t bytes[3] = {BT * nx * nx * 8, BT * nx * 8, BT * nx * 8};
+      for (int i = 0; i < 3; ++i) CU(cudaMalloc(&c->admm_scr[i], bytes[i]));
     }
-    if (admm_csqp_launch_x(c->k, *p, with_kkt, c->aplan, c->admm_scr, st) == 0)
-      return post_launch(c, "k_csqp_direction_admm");
+    if (c->admm_timing) { /* debug: per-phase clock64 cycles of CTA 0, printed after the launch (synchronises) */
+      CU(cudaMemsetAsync(c->admm_timing, 0, 8 * sizeof(long long), st));
+    }
+    if (admm_csqp_launch_x(c->k, *p, with_kkt, c->aplan, c->admm_scr, st, c->admm_timing) == 0) {
+      rc = post_launch(c, "k_csqp_direction_admm");
+      if (rc == MIMGPU_OK && c->admm_timing) {
+        long long h[8];
+        CU(cudaMemcpyAsync(h, c->admm_timing, sizeof(h), cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        fprintf(stderr, "mimgpu admm timing (cycles, CTA 0): ric %lld post_full %lld chain_bwd %lld gains %lld chain_fwd %lld update %lld\n",
+                h[0], h[1], h[2], h[3], h[4], h[5]);
+      }
+      return rc;
+    }
   }
   if (c->splan.ok && !c->force_generic && (al & 15) == 0 &&
       stream_csqp_launch_x(c->k, *p, with_kkt, c->splan, st) == 0)
