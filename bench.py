@@ -78,6 +78,19 @@ def make_workload(name: str, B: int, first: int, distinct: int) -> OCPBatch:
     return base if d == B else tile_batch(base, B)
 
 
+def base_config(name: str, B: int, default_tol: bool = False) -> dict:
+    """The `config` object both arms print (identical keys and values for the same workload)."""
+    w = WORKLOADS[name]
+    cfg = dict(CONFIGS[name])
+    nb = 8 * B * (cfg["T"] * (2 * cfg["nx"] ** 2 + 2 * cfg["nx"] * cfg["nu"] + cfg["nu"] ** 2) + cfg["nx"] ** 2)
+    return {"workload": name, "solver": w["solver"], **cfg, "B_per_gpu": B,
+            "l2": f"inputs >= {nb / 1e6:.0f} MB per step > 126 MB L2 (no flush needed)" if nb > 2 * 126e6
+                  else "inputs smaller than 2x L2",
+            "csqp_protocol": (("default tolerances (eps 1e-4, max 1000), cold start each step" if default_tol
+                               else f"eps_abs=eps_rel=0, {QP_ITERS} ADMM iterations, no eq. guess")
+                              if w["solver"] == "csqp" else None)}
+
+
 # ------------------------------------------------------------------ clocks sampler
 class ClockSampler:
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
@@ -192,15 +205,16 @@ def reference_arm(args, rank, world):
     if rank != 0:
         return
     w = WORKLOADS[args.workload]
-    sample = pick_cpu_sample(args.workload, w["solver"])
-    r = cpu_run(args.workload, w["solver"], sample, max(1, args.steps), max(1, args.warmup))
-    cfg = dict(CONFIGS[args.workload])
+    steps, warmup = max(1, args.steps), max(1, min(args.warmup, 3))
+    # bounded sample: the whole --steps K run ends within ~2 minutes whatever K is
+    sample = pick_cpu_sample(args.workload, w["solver"], target_s=min(1.5, 100.0 / (steps + warmup)))
+    r = cpu_run(args.workload, w["solver"], sample, steps, warmup)
     line = {
         "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": args.workload, "solver": w["solver"], **cfg, "B_per_step": sample},
-        "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",
+        "config": base_config(args.workload, args.batch or w["B"]),
+        "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample_B_per_step": sample,
                          "sample": f"{sample} problems of {args.workload} per step, oracle -O3 -march=native, "
                                    f"OpenMP over problems"},
         "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -211,121 +225,181 @@ def reference_arm(args, rank, world):
 
 
 # ------------------------------------------------------------------ GPU arm
-def gpu_arm(args, rank, world, local_rank):
+def fp64_peak(local_rank: int):
+    """FP64 roofline denominator: measured HERE by mimgpu_measure_peaks (register-resident DFMA loop);
+    profiles/peaks_r01.json only if the measurement fails.  MEASURED_PEAKS.json carries no FP64 figure."""
+    import ctypes as C
+    try:
+        lib = _capi.load_library()
+        a, b, c = C.c_double(), C.c_double(), C.c_double()
+        if lib.mimgpu_measure_peaks(local_rank, C.byref(a), C.byref(b), None) == 0 and a.value > 1.0:
+            return max(a.value, b.value), "mimgpu_measure_peaks in this run (DFMA %.1f / DMMA %.1f TFLOP/s)" % (a.value, b.value)
+    except Exception:
+        pass
+    f = ROOT / "profiles" / "peaks_r01.json"
+    if f.exists():
+        d = json.loads(f.read_text())
+        return float(max(d["dfma_tflops"], d["dmma_tflops"])), "profiles/peaks_r01.json"
+    return 37.0, "fallback 37 TFLOP/s"
+
+
+def traffic_entry(workload: str, B: int):
+    """dram bytes of one launch of the dominant kernel from the committed ncu --set full capture."""
+    for name in ("traffic_r02.json", "traffic_r01.json"):
+        tf = ROOT / "profiles" / name
+        if tf.exists():
+            tr = json.loads(tf.read_text()).get(workload)
+            if tr and tr.get("B") == B:
+                return tr
+    return None
+
+
+def run_workload(args, name, rank, world, local_rank, *, steps, warmup, e2e_steps, with_cpu, peaks):
+    """Device-resident arm + end-to-end arm (+ CPU arm on rank 0 at N = 1) of one workload."""
     import torch
     import torch.distributed as dist
     from mim_solvers_b200.engine import BatchEngine
 
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
-    torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
-    w = WORKLOADS[args.workload]
+    w = WORKLOADS[name]
     solver, B = w["solver"], (args.batch or w["B"])
-    cfg = dict(CONFIGS[args.workload])
-    batch = make_workload(args.workload, B, first=rank * B, distinct=args.distinct)
+    cfg = dict(CONFIGS[name])
+    batch = make_workload(name, B, first=rank * B, distinct=args.distinct)
     stream = torch.cuda.current_stream(dev)
     shape = batch.shape()
-
-    # --- device-resident arm: inputs live in HBM before the timed region
-    eng = BatchEngine(shape=shape, device=local_rank, stream=stream.cuda_stream)
-    dev_in = {k: torch.from_numpy(v).to(dev) for k, v in batch.arrays.items()}
-    eng.attach_device(dev_in)
-    if solver == "csqp":
-        p = csqp_bench_params()
-        eng.csqp_calc_norms()
-        eng.csqp_reset_rho(p)
-        step = lambda: eng.csqp_direction(p, with_kkt=True)
-    else:
-        p = _capi.default_sqp_params()
-        step = lambda: eng.sqp_direction(p, with_kkt=True)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize(dev)
 
-    for _ in range(args.warmup):
+    # --- device-resident arm: inputs live in HBM before the timed region, in the layout a device-side
+    # producer writes (knot records for the shapes that have them: no re-layout pass; else field-major)
+    eng = BatchEngine(shape=shape, device=local_rank, stream=stream.cuda_stream)
+    layout = "field-major"
+    dev_in = None
+    if solver == "sqp" and not args.field_major:
+        try:
+            eng.record_layout()
+            rec = torch.from_numpy(eng.pack_records(batch)).to(dev)
+            cost = torch.from_numpy(np.ascontiguousarray(batch.arrays["cost"])).to(dev)
+            eng.attach_records(rec, cost)
+            dev_in, layout = (rec, cost), "knot-records"
+        except _capi.MimGpuError:
+            pass
+    if dev_in is None:
+        dev_in = {k: torch.from_numpy(v).to(dev) for k, v in batch.arrays.items()}
+        eng.attach_device(dev_in)
+    if solver == "csqp":
+        p = csqp_bench_params() if not args.default_tol else _capi.default_csqp_params()
+        eng.csqp_calc_norms()
+        eng.csqp_reset_rho(p)
+        if args.default_tol:   # every step starts from the same cold solver state
+            step = lambda: (eng.csqp_reset_rho(p), eng.set_field("y", np.zeros(shape.field_shape("y"))),
+                            eng.csqp_direction(p, with_kkt=True))
+        else:
+            step = lambda: eng.csqp_direction(p, with_kkt=True)
+    else:
+        p = _capi.default_sqp_params()
+        step = lambda: eng.sqp_direction(p, with_kkt=True)
+
+    for _ in range(warmup):
         step()
     barrier()
     l0 = eng.launch_count
-    evs = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
     with ClockSampler(local_rank) as clk:
         barrier()
         evs[0].record(stream)
-        for i in range(args.steps):
+        for i in range(steps):
             step()
             evs[i + 1].record(stream)
         barrier()
     launches = eng.launch_count - l0
-    per = [evs[i].elapsed_time(evs[i + 1]) for i in range(args.steps)]
+    per = [evs[i].elapsed_time(evs[i + 1]) for i in range(steps)]
     total_ms = evs[0].elapsed_time(evs[-1])
     # SURVEY 8(e): the only collectives -- max time over ranks, batch-wide summary
     summ = allreduce_summary(eng.summary(1e-6), device=dev)
     total_ms = allreduce_max(total_ms, device=dev)
-    red = [summ["max_kkt"], summ["sum_qp_iters"], summ["n_converged"], summ["n_failed"]]
-    ms_per_step = total_ms / args.steps
+    ms_per_step = total_ms / steps
     value = world * B / (ms_per_step * 1e-3)
+    qp_iters_hist = None
+    if solver == "csqp":
+        it = eng.qp_iters
+        u, c = np.unique(it, return_counts=True)
+        qp_iters_hist = {int(a): int(b) for a, b in zip(u, c)}
 
     # --- roofline of the dominant kernel (one launch per step)
-    peaks_file = ROOT / "MEASURED_PEAKS.json"
-    if peaks_file.exists():
-        hbm_peak, peak_src = float(json.loads(peaks_file.read_text())["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs"
-    else:
-        hbm_peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    hbm_peak, hbm_src, f64_peak, f64_src = peaks
     kernel_ms = float(np.mean(per))
     bytes_qp = batch.algorithmic_bytes_per_qp()
-    flops_qp = batch.flops_csqp_qp(QP_ITERS, False) if solver == "csqp" else batch.flops_sqp_qp()
+    n_it = float(np.mean(eng.qp_iters)) if solver == "csqp" else 0.0
+    flops_qp = batch.flops_csqp_qp(int(round(min(n_it, p.max_qp_iters))), bool(p.equality_qp_initial_guess)) \
+        if solver == "csqp" else batch.flops_sqp_qp()
     ach_gbs = bytes_qp * B / (kernel_ms * 1e-3) / 1e9
+    tflops = flops_qp * B / (kernel_ms * 1e-3) / 1e12
     roof = {"bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": ach_gbs / hbm_peak,
-            "traffic": None, "peak_source": peak_src, "kernel_ms": kernel_ms,
-            "algorithmic_bytes_per_qp": bytes_qp, "flops_per_qp": flops_qp,
-            "fp64_tflops_achieved": flops_qp * B / (kernel_ms * 1e-3) / 1e12}
-    tf = ROOT / "profiles" / "traffic_r01.json"   # dram bytes of one launch from the committed ncu --set full capture
-    if tf.exists():
-        tr = json.loads(tf.read_text()).get(args.workload)
-        if tr and tr.get("B") == B:
-            roof["traffic"] = tr["dram_bytes_per_launch"]
-            roof["traffic_source"] = tr["source"]
-            roof["algorithmic_bytes_per_launch"] = bytes_qp * B
-    if solver == "csqp" or flops_qp / bytes_qp > 36.8e12 / (hbm_peak * 1e9):
-        roof.update(bound="fp64", achieved=roof["fp64_tflops_achieved"], peak=36.8, unit="TFLOP/s",
-                    frac=roof["fp64_tflops_achieved"] / 36.8,
-                    peak_source="mimgpu_measure_peaks DFMA loop on B200 (profiles/peaks_r01.json)")
+            "traffic": None, "peak_source": hbm_src, "kernel_ms": kernel_ms,
+            "algorithmic_bytes_per_qp": bytes_qp, "flops_per_qp": flops_qp, "fp64_tflops_achieved": tflops}
+    tr = traffic_entry(name, B)
+    if tr:
+        roof.update(traffic=tr["dram_bytes_per_launch"], traffic_source=tr["source"],
+                    algorithmic_bytes_per_launch=bytes_qp * B)
+    if flops_qp / bytes_qp > f64_peak * 1e12 / (hbm_peak * 1e9):
+        # SURVEY 8(d): above the machine balance the FP64 pipe is the binding roof of the algorithmic work
+        roof.update(bound="fp64", achieved=tflops, peak=f64_peak, unit="TFLOP/s", frac=tflops / f64_peak,
+                    peak_source=f64_src)
+    if solver == "csqp":
+        # what the ADMM sweeps actually stream: the iteration working set (SURVEY 8d), read once per sweep
+        T, nx, nu, ng = batch.T, batch.nx, batch.nu, batch.ng
+        ws = 8 * T * (nx * nx + 2 * nx * nu + nu * nu + ng * (nx + nu) + 6 * nx + 4 * nu + 6 * ng)
+        st_gbs = ws * n_it * B / (kernel_ms * 1e-3) / 1e9
+        roof["hbm_stream"] = {"iteration_working_set_bytes": ws, "mean_qp_iters": n_it,
+                              "achieved_gbs_one_read_per_iteration": st_gbs, "frac_of_hbm_peak": st_gbs / hbm_peak,
+                              "note": "the sequential sweeps need hundreds of problems in flight, whose working sets "
+                                      "(B_in_flight x ws) exceed L2: the loop streams from HBM (DESIGN.md 4.3)"}
 
     # --- end-to-end arm: host (pinned) buffers through the C ABI, copies inside the timed region
     e2e = None
-    if not args.no_e2e:
+    if e2e_steps > 0:
         del dev_in
         eng.close()
         torch.cuda.empty_cache()
         eng2 = BatchEngine(shape=shape, device=local_rank, stream=stream.cuda_stream)
-        pinned = OCPBatch(batch.B, batch.T, batch.nx, batch.nu, batch.ng, batch.ngT)
-        for k, v in batch.arrays.items():
-            t = torch.empty(v.shape, dtype=torch.float64).pin_memory()
-            t.numpy()[...] = v
-            pinned.arrays[k] = t.numpy()
-            pinned.arrays["_t_" + k] = t
-        keep = {k: pinned.arrays.pop(k) for k in list(pinned.arrays) if k.startswith("_t_")}
+
+        def pin(a):
+            t = torch.empty(a.shape, dtype=torch.float64).pin_memory()
+            t.numpy()[...] = a
+            return t
+        use_rec = layout == "knot-records"
+        if use_rec:
+            prec, pcost = pin(eng2.pack_records(batch)), pin(batch.arrays["cost"])
+            h2d = prec.numel() * 8 + pcost.numel() * 8
+        else:
+            pinned = OCPBatch(batch.B, batch.T, batch.nx, batch.nu, batch.ng, batch.ngT)
+            keep = {k: pin(v) for k, v in batch.arrays.items()}
+            pinned.arrays = {k: t.numpy() for k, t in keep.items()}
+            h2d = sum(v.nbytes for v in pinned.arrays.values())
         outs = {n: torch.empty(tuple(shape.field_shape(n)), dtype=torch.float64).pin_memory()
                 for n in (("dx_tilde", "du_tilde", "lag_mul", "y", "z") if solver == "csqp"
                           else ("dx", "du", "lag_mul"))}
         kkt = torch.empty(B, dtype=torch.float64).pin_memory()
-        h2d = sum(v.nbytes for v in pinned.arrays.values())
         d2h = sum(t.numel() * 8 for t in outs.values()) + B * 8
 
         def e2e_step():
-            if solver == "sqp":   # upload + direction + download in overlapped slices, one C-ABI call
+            if solver == "sqp" and use_rec:   # upload + direction + download in overlapped slices, one C-ABI call
+                eng2.sqp_direction_host_records(prec.numpy(), pcost.numpy(), p, dx=outs["dx"].numpy(),
+                                                du=outs["du"].numpy(), lag_mul=outs["lag_mul"].numpy(),
+                                                kkt=kkt.numpy(), n_chunks=args.e2e_chunks)
+                return
+            if solver == "sqp":
                 eng2.sqp_direction_host(pinned, p, dx=outs["dx"].numpy(), du=outs["du"].numpy(),
                                         lag_mul=outs["lag_mul"].numpy(), kkt=kkt.numpy(), n_chunks=args.e2e_chunks)
                 return
             eng2.upload(pinned)
-            if solver == "csqp":
-                eng2.csqp_calc_norms()
-                eng2.csqp_reset_rho(p)
-                eng2.csqp_direction(p, with_kkt=True)
-            else:
-                eng2.sqp_direction(p, with_kkt=True)
+            eng2.csqp_calc_norms()
+            eng2.csqp_reset_rho(p)
+            eng2.csqp_direction(p, with_kkt=True)
             for n, t in outs.items():
                 if t.numel():
                     eng2.download_into(n, t.numpy())
@@ -333,52 +407,109 @@ def gpu_arm(args, rank, world, local_rank):
                                                eng2.stream), "mimgpu_scalar")
             eng2.sync()
 
-        n_e2e = max(2, min(args.steps, args.e2e_steps))
         for _ in range(2):
             e2e_step()
         barrier()
         t0 = time.perf_counter()
-        for _ in range(n_e2e):
+        for _ in range(e2e_steps):
             e2e_step()
         barrier()
-        dt = allreduce_max((time.perf_counter() - t0) / n_e2e, device=dev)
+        dt = allreduce_max((time.perf_counter() - t0) / e2e_steps, device=dev)
         e2e = {"value": world * B / dt, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
-               "d2h_bytes_per_step": int(d2h), "ms_per_step": dt * 1e3, "steps": n_e2e,
-               "call": "mimgpu_sqp_direction_host (%d overlapped slices)" % args.e2e_chunks if solver == "sqp"
+               "d2h_bytes_per_step": int(d2h), "ms_per_step": dt * 1e3, "steps": e2e_steps,
+               "h2d_gbs_per_rank": h2d / dt / 1e9,
+               "call": ("mimgpu_sqp_direction_host_records" if use_rec else "mimgpu_sqp_direction_host")
+                       + " (%d overlapped slices)" % args.e2e_chunks if solver == "sqp"
                        else "mimgpu_upload + csqp_direction + mimgpu_download",
                "max_kkt": float(kkt.max())}
-        del keep
+        eng2.close()
+        torch.cuda.empty_cache()
+    else:
+        eng.close()
 
+    cpu = None
+    if with_cpu and rank == 0 and world == 1:
+        sample = pick_cpu_sample(name, solver, target_s=1.0)
+        r = cpu_run(name, solver, sample, 5, 1)
+        s1 = max(8, sample // max(1, r["cores"]) // 8 * 8)
+        r1 = cpu_run(name, solver, s1, 3, 1, nthreads=1)
+        cpu = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",
+               "sample": f"{sample} problems of {name} x 5 passes, CPU oracle (-O3 -march=native, "
+                         f"OpenMP over problems)",
+               "single_thread": {"value": r1["value"], "cores": 1, "sample": f"{s1} problems x 3 passes"}}
+    return {
+        "value": value, "unit": UNIT, "ms_per_step": ms_per_step, "steps": steps, "warmup": warmup,
+        "config": base_config(name, B, args.default_tol),
+        "config_detail": {"input_layout": layout, "distinct_problems_per_gpu": min(B, args.distinct),
+                          "input_bytes_per_step": batch.nbytes()},
+        "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
+        "qp_iters_histogram": qp_iters_hist, "clocks": clk.summary(),
+        "batch_summary": {"max_kkt": float(summ["max_kkt"]), "sum_qp_iters": int(summ["sum_qp_iters"]),
+                          "n_converged": int(summ["n_converged"]), "n_failed": int(summ["n_failed"])},
+    }
+
+
+def gpu_arm(args, rank, world, local_rank):
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    bind_rank_to_numa(local_rank)
+    peaks_file = ROOT / "MEASURED_PEAKS.json"
+    if peaks_file.exists():
+        hbm_peak, hbm_src = float(json.loads(peaks_file.read_text())["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs"
+    else:
+        hbm_peak, hbm_src = 6650.0, "fallback (B200_PROFILING.md)"
+    f64_peak, f64_src = fp64_peak(local_rank)
+    peaks = (hbm_peak, hbm_src, f64_peak, f64_src)
+    main = run_workload(args, args.workload, rank, world, local_rank, steps=args.steps, warmup=args.warmup,
+                        e2e_steps=0 if args.no_e2e else max(2, min(args.steps, args.e2e_steps)),
+                        with_cpu=not args.no_cpu, peaks=peaks)
+    extra = {}
+    for name in ([] if args.no_extra else [w for w in args.extra.split(",") if w and w != args.workload]):
+        r = run_workload(args, name, rank, world, local_rank, steps=args.extra_steps, warmup=3,
+                         e2e_steps=0 if args.no_e2e else 2, with_cpu=not args.no_cpu, peaks=peaks)
+        extra[name] = {k: r[k] for k in ("value", "unit", "ms_per_step", "steps", "config", "config_detail", "roofline", "cpu_baseline",
+                                          "e2e", "gpu_launches", "qp_iters_histogram", "batch_summary")}
     if rank != 0:
         return
-    cpu = None
-    if not args.no_cpu and world == 1:
-        sample = pick_cpu_sample(args.workload, solver, target_s=1.0)
-        r = cpu_run(args.workload, solver, sample, 10, 2)
-        cpu = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",
-               "sample": f"{sample} problems of {args.workload} x 10 passes, CPU oracle (-O3 -march=native, "
-                         f"OpenMP over problems)"}
     line = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": args.workload, "solver": solver, **cfg, "B_per_gpu": B,
-                   "distinct_problems_per_gpu": min(B, args.distinct),
-                   "l2": f"inputs {batch.nbytes() / 1e6:.0f} MB per step > 126 MB L2 (no flush needed)"
-                         if batch.nbytes() > 2 * 126e6 else "inputs smaller than 2x L2",
-                   "csqp_protocol": f"eps_abs=eps_rel=0, {QP_ITERS} ADMM iterations, no eq. guess" if solver == "csqp" else None},
-        "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
-        "clocks": clk.summary(),
-        "batch_summary": {"max_kkt": float(red[0]), "sum_qp_iters": int(red[1]), "n_converged": int(red[2]),
-                          "n_failed": int(red[3])},
+        "metric": METRIC, "value": main["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": main["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": main["config"],
+        "config_detail": main["config_detail"],
+        "roofline": main["roofline"], "cpu_baseline": main["cpu_baseline"], "e2e": main["e2e"],
+        "gpu_launches": main["gpu_launches"], "clocks": main["clocks"], "batch_summary": main["batch_summary"],
+        "workloads": extra,
     }
+    if main["qp_iters_histogram"]:
+        line["qp_iters_histogram"] = main["qp_iters_histogram"]
     print(json.dumps(line), flush=True)
+
+
+def bind_rank_to_numa(local_rank: int):
+    """Pin this rank's threads (and therefore its first-touch pinned allocations and copy threads) to
+    the CPUs nearest to its GPU, when the box exposes more than one NUMA node (nvidia-smi topo)."""
+    try:
+        import pynvml as nv
+        nv.nvmlInit()
+        h = nv.nvmlDeviceGetHandleByIndex(local_rank)
+        mask = nv.nvmlDeviceGetCpuAffinity(h, max(1, ((os.cpu_count() or 64) + 63) // 64))
+        cpus = [64 * i + b for i, m in enumerate(mask) for b in range(64) if (m >> b) & 1]
+        world = int(os.environ.get("LOCAL_WORLD_SIZE", os.environ.get("WORLD_SIZE", "1")))
+        if cpus and world > 1:   # split the GPU's CPU set among the ranks that share it
+            share = [c for i, c in enumerate(sorted(cpus)) if i % world == local_rank % world] or cpus
+            os.sched_setaffinity(0, share)
+        elif cpus:
+            os.sched_setaffinity(0, cpus)
+    except Exception:
+        pass
 
 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=600)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="C2_ur5_sqp", choices=sorted(WORKLOADS))
@@ -387,6 +518,14 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--e2e-chunks", type=int, default=8, help="slices of the overlapped host path (SQP)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--extra", default="C3_solo12_csqp",
+                    help="comma-separated workloads reported in the `workloads` sub-dict of the line")
+    ap.add_argument("--extra-steps", type=int, default=5)
+    ap.add_argument("--no-extra", action="store_true")
+    ap.add_argument("--field-major", action="store_true",
+                    help="device-resident SQP inputs in the field-major layout (re-laid-out inside every step)")
+    ap.add_argument("--default-tol", action="store_true",
+                    help="CSQP at the default tolerances (eps 1e-4, max 1000 iterations) instead of the 50-iteration protocol")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--qp-iters", type=int, default=50, help="ADMM iterations per CSQP QP (protocol: 50)")
     args = ap.parse_args()
