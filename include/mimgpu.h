@@ -164,7 +164,9 @@ enum mimgpu_field {
   MIMGPU_F_QU = 12,       /* Qu_        [B][T][nu]    */
   MIMGPU_F_QUUK = 13,     /* Quuk_      [B][T][nu]    (SQP/FDDP only) */
   MIMGPU_F_QUU_LLT = 14,  /* lower Cholesky factor of Quu_ [B][T][nu*nu] col-major */
-  MIMGPU_F_COUNT = 15
+  MIMGPU_F_XS = 15,       /* xs_        [B][T+1][nx]  (device-side solve(): mimgpu_sqp_solve) */
+  MIMGPU_F_US = 16,       /* us_        [B][T][nu]    */
+  MIMGPU_F_COUNT = 17
 };
 
 /* Per-problem scalars ([B] each). */
@@ -182,7 +184,10 @@ enum mimgpu_scalar {
   MIMGPU_S_CONSTRAINT_NORM = 10,
   MIMGPU_S_DG = 11,            /* FDDP dg_ (src/fddp.cpp:256-279) */
   MIMGPU_S_DQ = 12,            /* FDDP dq_ */
-  MIMGPU_S_COUNT = 13
+  MIMGPU_S_COST = 13,          /* cost_       (device-side solve()) */
+  MIMGPU_S_STEPLENGTH = 14,    /* steplength_ of the last line search */
+  MIMGPU_S_PREG = 15,          /* preg_ = dreg_ */
+  MIMGPU_S_COUNT = 16
 };
 
 /* Batch-wide summary (the quantities of SURVEY 8(e) all-reduce). */
@@ -296,6 +301,53 @@ int mimgpu_csqp_reset_rho(mimgpu_ctx* ctx, const mimgpu_csqp_params* p,
  * (max_qp_iters+1 on exhaustion). */
 int mimgpu_csqp_direction(mimgpu_ctx* ctx, const mimgpu_csqp_params* p,
                           int with_kkt, void* cuda_stream);
+
+/* ---- solve() on the device (analytic models) -------------------------------- */
+/* For problems whose running / terminal models can be evaluated on the GPU the whole
+ * SolverSQP::solve (src/sqp.cpp:75-222) runs there: model calc / calcDiff, computeDirection,
+ * checkKKTConditions, the merit / filter line search over alphas_ = 2^-n (tryStep,
+ * src/sqp.cpp:307-374), setCandidate and the regularisation schedule (src/ddp.cpp:431-445), with
+ * one iteration counter, filter memory and regularisation per problem.  No derivative ever
+ * crosses PCIe; the host reads two counters per SQP iteration.
+ *
+ * Model family (LQ plus separable polynomial terms; c3 = w4 = 0 is the ActionModelLQR of the
+ * reference's fixtures, tests/python/problems.py, tests/test_solvers.cpp:255-300):
+ *     x+  = A_t x + B_t u + f_t + c3 x^3            l_T = 1/2 x^T Q_T x + q_T.x + w4/4 sum x_i^4
+ *     l_t = 1/2 [x;u]^T [[Q,S],[S^T,R]] [x;u] + q.x + r.u + w4/4 sum x_i^4
+ * Arrays in the block layouts of the derivative struct: A like Fx, Bm like Fu, Q S R like Lxx Lxu Luu. */
+typedef struct {
+  const double *A, *Bm, *f;        /* [B][T][nx*nx], [B][T][nx*nu], [B][T][nx] */
+  const double *Q, *S, *R, *q, *r; /* [B][T][nx*nx], [B][T][nx*nu], [B][T][nu*nu], [B][T][nx], [B][T][nu] */
+  const double *QT, *qT;           /* [B][nx*nx], [B][nx] */
+  const double* x0;                /* [B][nx] problem_->get_x0() */
+  double c3, w4;
+} mimgpu_poly_model;
+
+typedef struct {                   /* members of SolverSQP / SolverDDP that steer solve() */
+  int32_t maxiter;                 /* 100 */
+  int32_t use_filter_line_search;  /* 1   (include/mim_solvers/sqp.hpp:164-181) */
+  int32_t filter_size;             /* 1   (<= 16) */
+  int32_t extra_iteration_for_last_kkt; /* 0 */
+  double reg_init;                 /* NaN -> reg_min (src/sqp.cpp:91-97) */
+  double reg_min, reg_max;         /* 1e-9, 1e9 (src/ddp.cpp:27-28) */
+  double reg_incfactor, reg_decfactor; /* 10, 10 */
+  double th_stepdec, th_stepinc;   /* 0.5, 0.01 */
+  double termination_tol;          /* 1e-6 */
+  double mu_dynamic;               /* 1.0 */
+} mimgpu_sqp_solve_params;
+
+/* Gives the ctx its model (ng = ngT = 0).  MIMGPU_MEM_HOST: copied; MIMGPU_MEM_DEVICE: attached. */
+int mimgpu_model_attach(mimgpu_ctx* ctx, const mimgpu_poly_model* model, int memkind, void* cuda_stream);
+/* SolverSQP::solve(init_xs, init_us, maxiter, false, reg_init) for all B problems.  xs0 [B][T+1][nx],
+ * us0 [B][T][nu] are HOST arrays (NULL = zeros, as crocoddyl's setCandidate).  Synchronous.  Results:
+ * MIMGPU_F_XS / MIMGPU_F_US, the members of the last computeDirection, MIMGPU_S_KKT / _COST / _MERIT /
+ * _GAP_NORM / _STEPLENGTH / _PREG, mimgpu_solve_info.  *n_sqp_iters (may be NULL) = iterations of the
+ * slowest problem. */
+int mimgpu_sqp_solve(mimgpu_ctx* ctx, const mimgpu_sqp_solve_params* p, const double* xs0, const double* us0,
+                     int32_t* n_sqp_iters, void* cuda_stream);
+/* iter_ [B] and the outcome [B] (1 = solve() returned true, 2 = false by regularisation limit, 0 = false by
+ * maxiter) of the last mimgpu_sqp_solve; either may be NULL. */
+int mimgpu_solve_info(mimgpu_ctx* ctx, int32_t* iters, int32_t* outcome, void* cuda_stream);
 
 /* ---- data out -------------------------------------------------------------- */
 /* Copies one solver member of all B problems to host memory `dst`

@@ -24,14 +24,14 @@ MEM_HOST, MEM_DEVICE = 0, 1
 
 FIELDS = dict(
     dx=0, du=1, lag_mul=2, dx_tilde=3, du_tilde=4, y=5, z=6, rho_vec=7,
-    Vxx=8, Vx=9, K=10, k=11, Qu=12, Quuk=13, Quu_llt=14,
+    Vxx=8, Vx=9, K=10, k=11, Qu=12, Quuk=13, Quu_llt=14, xs=15, us=16,
 )
 SCALARS = dict(
     KKT=0, gap_norm=1, merit=2, x_grad_norm=3, u_grad_norm=4, norm_primal=5,
     norm_dual=6, norm_primal_rel=7, norm_dual_rel=8, rho_sparse=9,
-    constraint_norm=10, dg=11, dq=12,
+    constraint_norm=10, dg=11, dq=12, cost=13, steplength=14, preg=15,
 )
-N_SCALARS = 13
+N_SCALARS = 16
 
 
 class Shape(C.Structure):
@@ -48,6 +48,7 @@ class Shape(C.Structure):
             "Vxx": (B, T + 1, nx, nx), "Vx": (B, T + 1, nx),
             "K": (B, T, nu, nx), "k": (B, T, nu), "Qu": (B, T, nu),
             "Quuk": (B, T, nu), "Quu_llt": (B, T, nu, nu),
+            "xs": (B, T + 1, nx), "us": (B, T, nu),
         }[name]
 
 
@@ -77,6 +78,31 @@ class RecordLayout(C.Structure):
     _fields_ = [(n, C.c_int32) for n in (
         "rec_doubles", "term_doubles", "problem_doubles", "off_fs", "off_Lxx", "off_Lxu", "off_Luu",
         "off_Lx", "off_Lu", "off_Fx", "off_Fu", "toff_fs", "toff_Lxx", "toff_Lx")] + [("reserved", C.c_int32 * 2)]
+
+
+class PolyModel(C.Structure):
+    """mimgpu_poly_model: analytic model of the device-side solve()."""
+    _fields_ = [(n, C.c_void_p) for n in ("A", "Bm", "f", "Q", "S", "R", "q", "r", "QT", "qT", "x0")] + [
+        ("c3", C.c_double), ("w4", C.c_double)]
+
+
+class SqpSolveParams(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("maxiter", "use_filter_line_search", "filter_size",
+                                         "extra_iteration_for_last_kkt")] + [(n, C.c_double) for n in (
+        "reg_init", "reg_min", "reg_max", "reg_incfactor", "reg_decfactor", "th_stepdec", "th_stepinc",
+        "termination_tol", "mu_dynamic")]
+
+
+def default_sqp_solve_params(**kw) -> SqpSolveParams:
+    """Defaults of src/ddp.cpp:25-32 and include/mim_solvers/sqp.hpp:164-181."""
+    d = dict(maxiter=100, use_filter_line_search=1, filter_size=1, extra_iteration_for_last_kkt=0,
+             reg_init=float("nan"), reg_min=1e-9, reg_max=1e9, reg_incfactor=10.0, reg_decfactor=10.0,
+             th_stepdec=0.5, th_stepinc=0.01, termination_tol=1e-6, mu_dynamic=1.0)
+    for k, v in kw.items():
+        if k not in d:
+            raise TypeError(f"unknown solve parameter {k!r}")
+        d[k] = type(d[k])(v)
+    return SqpSolveParams(**d)
 
 
 class Summary(C.Structure):
@@ -114,7 +140,7 @@ SYMBOLS = (
     "mimgpu_destroy", "mimgpu_get_shape", "mimgpu_upload", "mimgpu_set_reg",
     "mimgpu_set_active", "mimgpu_set_field", "mimgpu_sqp_direction",
     "mimgpu_sqp_direction_host", "mimgpu_sqp_direction_host_records", "mimgpu_get_record_layout",
-    "mimgpu_upload_records", "mimgpu_fddp_direction", "mimgpu_csqp_calc_norms", "mimgpu_csqp_reset_rho",
+    "mimgpu_upload_records", "mimgpu_model_attach", "mimgpu_sqp_solve", "mimgpu_solve_info", "mimgpu_fddp_direction", "mimgpu_csqp_calc_norms", "mimgpu_csqp_reset_rho",
     "mimgpu_csqp_direction", "mimgpu_download", "mimgpu_field_ptr", "mimgpu_scalar",
     "mimgpu_iters_status", "mimgpu_converged", "mimgpu_summary_reduce", "mimgpu_launch_count", "mimgpu_stream_sync", "mimgpu_measure_peaks",
 )
@@ -140,6 +166,9 @@ def _declare(lib):
     lib.mimgpu_sqp_direction_host_records.argtypes = [vp, vp, vp, C.POINTER(SqpParams), vp, vp, vp, vp, i32]
     lib.mimgpu_get_record_layout.argtypes = [vp, C.POINTER(RecordLayout)]
     lib.mimgpu_upload_records.argtypes = [vp, vp, vp, C.c_int, vp]
+    lib.mimgpu_model_attach.argtypes = [vp, C.POINTER(PolyModel), C.c_int, vp]
+    lib.mimgpu_sqp_solve.argtypes = [vp, C.POINTER(SqpSolveParams), vp, vp, C.POINTER(i32), vp]
+    lib.mimgpu_solve_info.argtypes = [vp, vp, vp, vp]
     lib.mimgpu_fddp_direction.argtypes = [vp, C.POINTER(SqpParams), vp]
     lib.mimgpu_csqp_calc_norms.argtypes = [vp, vp]
     lib.mimgpu_csqp_reset_rho.argtypes = [vp, C.POINTER(CsqpParams), vp]

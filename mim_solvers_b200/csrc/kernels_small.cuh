@@ -495,6 +495,9 @@ __global__ void __launch_bounds__(WPB * 32, SmallTune<NX, NU>::MINB) k_sqp_direc
     st = small_backward_mma<NX, NU>(p, sw, lane, preg, dreg, kp.is_feasible);
   else
     st = small_backward<NX, NU>(p, sw, lane, preg, dreg, kp.is_feasible);
+  /* pad_ bit 0: members-only rerun (the C ABI asks for Qu_ / Quuk_ / Quu_llt_ after a fast launch):
+   * the direction, the scalars and the status word of the fast launch stay as they are */
+  if (a.pad_ & 1) { cp_async_wait<0>(); return; }
   if (lane == 0) { a.status[b] = st; a.qp_iters[b] = 0; }
   if (st) {
     cp_async_wait<0>();

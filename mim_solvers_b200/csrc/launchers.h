@@ -40,6 +40,39 @@ int stream_csqp_launch_x(const KArgs& a, const mimgpu_csqp_params& q, int with_k
 AdmmPlan admm_plan_x(const mimgpu_shape& sh, int stage_fx, int max_smem);
 int admm_csqp_launch_x(const KArgs& a, const mimgpu_csqp_params& q, int with_kkt, const AdmmPlan& pl,
                        double* const scratch[3], cudaStream_t st, long long* timing = nullptr);
+/* device-side solve() for analytic models (kernels_solve.cuh) */
+constexpr int SOLVE_NALPHA = 10;   /* alphas_ = 2^-n, n = 0..9 (src/sqp.cpp:60-70) */
+constexpr int SOLVE_MAXFILTER = 16;
+
+struct PolyModelDev { /* device pointers, C-ABI block layouts (col-major), leading [B][T] */
+  const double *A, *Bm, *f, *Q, *S, *R, *q, *r, *QT, *qT, *x0;
+  double c3, w4;
+};
+
+struct SolveDev {
+  double *xs, *us;                 /* [B][T+1][nx], [B][T][nu] */
+  double *cost, *steplength;       /* [B] */
+  double *cost_list, *gap_list;    /* [B][filter_size]: index filter_size-1 = newest */
+  double *preg, *dreg;             /* [B] */
+  int32_t *iter, *done, *flag;     /* [B]; done: 0 running, 1 converged, 2 failed; flag: 1 = retry direction */
+  int32_t *list_a, *list_b;        /* [B] compacted problem lists */
+  int32_t* counts;                 /* [4] */
+};
+
+struct SolvePar {
+  double reg_min, reg_max, reg_inc, reg_dec, th_stepdec, th_stepinc, termination_tol, mu_dynamic;
+  int use_filter, filter_size;
+};
+
+int solve_init_launch_x(const SolveDev& s, const PolyModelDev& m, const double* xs0, const double* us0,
+                        const mimgpu_shape& sh, double reg0, cudaStream_t st);
+int solve_calcdiff_launch_x(const KArgs& a, const PolyModelDev& m, const SolveDev& s, const int32_t* list, int n,
+                            cudaStream_t st);
+int solve_post_direction_launch_x(const KArgs& a, const SolveDev& s, const SolvePar& sp, const int32_t* list, int n,
+                                  int32_t* retry_out, cudaStream_t st);
+int solve_linesearch_launch_x(const KArgs& a, const PolyModelDev& m, const SolveDev& s, const SolvePar& sp,
+                              const int32_t* list, int n, cudaStream_t st);
+int solve_running_launch_x(const SolveDev& s, int B, cudaStream_t st);
 /* CTA-per-problem DMMA SQP / FDDP kernel (kernels_ric.cuh, kernels_cta.cuh) */
 CtaPlan cta_plan_x(const mimgpu_shape& sh, int stage_fx, int max_smem);
 int cta_sqp_launch_x(const KArgs& a, const SqpKPar& kp, bool fddp, const CtaPlan& pl, cudaStream_t st);

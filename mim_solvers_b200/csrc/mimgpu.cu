@@ -8,11 +8,13 @@
  */
 #include <cuda_runtime.h>
 
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "launchers.h"
@@ -77,6 +79,13 @@ struct mimgpu_ctx {
   bool fields_valid = true;        /* records mode: the field-major arrays have been rebuilt from the records */
   double* cost_buf = nullptr;      /* [B] cost_ of host-side record uploads */
   cudaStream_t last_stream = nullptr; /* stream of the last asynchronous call (ordering of the chunked host path) */
+  /* device-side solve() (mimgpu_model_attach / mimgpu_sqp_solve) */
+  PolyModelDev model{};
+  double* model_buf = nullptr;     /* owned copy of a host-side model */
+  bool have_model = false;
+  SolveDev sv{};
+  void* solve_buf = nullptr;       /* iter, done, flag, two lists, counters, filter memory */
+  int solve_filter_size = 0;
 };
 
 static size_t deriv_sizes(const mimgpu_shape& s, size_t n[20]) {
@@ -130,6 +139,8 @@ static void field_sizes(const mimgpu_shape& s, size_t n[MIMGPU_F_COUNT]) {
   n[MIMGPU_F_QU] = B * T * nu;
   n[MIMGPU_F_QUUK] = B * T * nu;
   n[MIMGPU_F_QUU_LLT] = B * T * nu * nu;
+  n[MIMGPU_F_XS] = B * (T + 1) * nx;
+  n[MIMGPU_F_US] = B * T * nu;
 }
 
 /* ------------------------------------------------------------------ kernels */
@@ -330,7 +341,7 @@ void mimgpu_destroy(mimgpu_ctx* c) {
   if (c->pipe_st[0]) cudaStreamDestroy(c->pipe_st[0]);
   if (c->pipe_st[1]) cudaStreamDestroy(c->pipe_st[1]);
   for (int i = 0; i < 3; ++i) cudaFree(c->admm_scr[i]);
-  cudaFree(c->cost_buf); cudaFree(c->admm_timing);
+  cudaFree(c->cost_buf); cudaFree(c->admm_timing); cudaFree(c->model_buf); cudaFree(c->solve_buf);
   cudaFree(c->pack_buf); cudaFree(c->spill_buf); cudaFree(c->in_buf); cudaFree(c->state_buf); cudaFree(c->ibuf); cudaFree(c->reg_buf); cudaFree(c->summary_dev);
   delete c;
 }
@@ -800,6 +811,188 @@ int mimgpu_csqp_direction(mimgpu_ctx* c, const mimgpu_csqp_params* p, int with_k
   return post_launch(c, "k_csqp_direction_generic");
 }
 
+/* ------------------------------------------------------ solve() on the device */
+int mimgpu_model_attach(mimgpu_ctx* c, const mimgpu_poly_model* m, int memkind, void* stream) {
+  if (!c || !m) return fail(MIMGPU_ERR_INVALID, "null pointer");
+  if (c->sh.ng || c->sh.ngT) return fail(MIMGPU_ERR_UNSUPPORTED, "device-side solve(): unconstrained models only (ng = ngT = 0)");
+  cudaStream_t st = (cudaStream_t)stream;
+  CU(cudaSetDevice(c->device));
+  const size_t B = c->sh.B, T = c->sh.T, nx = c->sh.nx, nu = c->sh.nu;
+  const size_t n[11] = {B * T * nx * nx, B * T * nx * nu, B * T * nx, B * T * nx * nx, B * T * nx * nu, B * T * nu * nu,
+                        B * T * nx, B * T * nu, B * nx * nx, B * nx, B * nx};
+  const double* src[11] = {m->A, m->Bm, m->f, m->Q, m->S, m->R, m->q, m->r, m->QT, m->qT, m->x0};
+  for (int i = 0; i < 11; ++i)
+    if (n[i] && !src[i]) return fail(MIMGPU_ERR_INVALID, "missing model array #" + std::to_string(i));
+  const double* dev[11];
+  if (memkind == MIMGPU_MEM_DEVICE) {
+    for (int i = 0; i < 11; ++i) dev[i] = src[i];
+  } else if (memkind == MIMGPU_MEM_HOST) {
+    size_t tot = 0;
+    for (int i = 0; i < 11; ++i) tot += (n[i] + 1) & ~(size_t)1;
+    if (!c->model_buf) CU(cudaMalloc(&c->model_buf, tot * sizeof(double)));
+    double* q = c->model_buf;
+    for (int i = 0; i < 11; ++i) {
+      if (n[i]) CU(cudaMemcpyAsync(q, src[i], n[i] * sizeof(double), cudaMemcpyHostToDevice, st));
+      dev[i] = q;
+      q += (n[i] + 1) & ~(size_t)1;
+    }
+  } else {
+    return fail(MIMGPU_ERR_INVALID, "bad memkind");
+  }
+  PolyModelDev& d = c->model;
+  d.A = dev[0]; d.Bm = dev[1]; d.f = dev[2]; d.Q = dev[3]; d.S = dev[4]; d.R = dev[5]; d.q = dev[6]; d.r = dev[7];
+  d.QT = dev[8]; d.qT = dev[9]; d.x0 = dev[10]; d.c3 = m->c3; d.w4 = m->w4;
+  /* the derivative arrays the direction kernels read live in the ctx's own buffer: the constant blocks
+   * (Fx = A, Fu = B, Lxx = Q, Lxu = S, Luu = R, LxxT = QT) are copied once, k_model_calcdiff fills the rest */
+  size_t dn[20];
+  int rc = ensure_in_buf(c, dn);
+  if (rc) return rc;
+  const double** slot[20];
+  deriv_slots(c->k, slot);
+  double* q = c->in_buf;
+  double* at[20];
+  for (int i = 0; i < 20; ++i) { at[i] = q; *slot[i] = dn[i] ? q : nullptr; q += (dn[i] + 1) & ~(size_t)1; }
+  const int map[6][2] = {{0, 0}, {1, 1}, {2, 3}, {3, 4}, {4, 5}, {8, 8}}; /* deriv slot <- model array */
+  for (auto& mm : map)
+    if (dn[mm[0]]) CU(cudaMemcpyAsync(at[mm[0]], dev[mm[1]], dn[mm[0]] * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  c->have_model = true;
+  c->attached = false; c->records_mode = false; c->fields_valid = true; c->k.pack = nullptr; c->pack_dirty = true;
+  c->last_stream = st;
+  inputs_changed(c);
+  return MIMGPU_OK;
+}
+
+static int solve_alloc(mimgpu_ctx* c, int filter_size) {
+  const size_t B = c->sh.B;
+  if (c->solve_buf && c->solve_filter_size == filter_size) return MIMGPU_OK;
+  cudaFree(c->solve_buf);
+  c->solve_buf = nullptr;
+  const size_t bytes = (5 * B + 4) * sizeof(int32_t) + 8 + 2 * B * (size_t)filter_size * sizeof(double);
+  CU(cudaMalloc(&c->solve_buf, bytes));
+  CU(cudaMemset(c->solve_buf, 0, bytes)); /* the filter ring buffers start at 0 and persist across solve() calls */
+  c->solve_filter_size = filter_size;
+  SolveDev& s = c->sv;
+  double* dl = (double*)c->solve_buf;
+  s.cost_list = dl; s.gap_list = dl + B * filter_size;
+  int32_t* ip = (int32_t*)(dl + 2 * B * filter_size);
+  s.iter = ip; s.done = ip + B; s.flag = ip + 2 * B; s.list_a = ip + 3 * B; s.list_b = ip + 4 * B; s.counts = ip + 5 * B;
+  s.xs = c->field[MIMGPU_F_XS]; s.us = c->field[MIMGPU_F_US];
+  s.cost = c->k.scal + (size_t)MIMGPU_S_COST * B;
+  s.steplength = c->k.scal + (size_t)MIMGPU_S_STEPLENGTH * B;
+  s.preg = c->k.scal + (size_t)MIMGPU_S_PREG * B;
+  s.dreg = s.preg; /* dreg_ = preg_ throughout (src/ddp.cpp:431-445) */
+  return MIMGPU_OK;
+}
+
+int mimgpu_sqp_solve(mimgpu_ctx* c, const mimgpu_sqp_solve_params* p, const double* xs0, const double* us0,
+                     int32_t* n_sqp_iters, void* stream) {
+  if (!c || !p) return fail(MIMGPU_ERR_INVALID, "null pointer");
+  if (!c->have_model) return fail(MIMGPU_ERR_STATE, "mimgpu_sqp_solve before mimgpu_model_attach");
+  if (p->filter_size < 1 || p->filter_size > SOLVE_MAXFILTER || p->maxiter < 0)
+    return fail(MIMGPU_ERR_INVALID, "bad solve parameters");
+  cudaStream_t st = (cudaStream_t)stream;
+  CU(cudaSetDevice(c->device));
+  int rc = solve_alloc(c, p->filter_size);
+  if (rc) return rc;
+  const mimgpu_shape& sh = c->sh;
+  const int B = sh.B;
+  SolveDev& s = c->sv;
+  const size_t nxs = c->field_n[MIMGPU_F_XS], nus = c->field_n[MIMGPU_F_US];
+  if (xs0) CU(cudaMemcpyAsync(s.xs, xs0, nxs * sizeof(double), cudaMemcpyHostToDevice, st));
+  else CU(cudaMemsetAsync(s.xs, 0, nxs * sizeof(double), st));
+  if (nus) {
+    if (us0) CU(cudaMemcpyAsync(s.us, us0, nus * sizeof(double), cudaMemcpyHostToDevice, st));
+    else CU(cudaMemsetAsync(s.us, 0, nus * sizeof(double), st));
+  }
+  const double reg0 = std::isnan(p->reg_init) ? p->reg_min : p->reg_init;
+  solve_init_launch_x(s, c->model, s.xs, s.us, sh, reg0, st); /* xs_[0] = x0, preg_ = dreg_ = reg0, iter_ = 0 */
+  c->launches++;
+  SolvePar sp{p->reg_min, p->reg_max, p->reg_incfactor, p->reg_decfactor, p->th_stepdec, p->th_stepinc,
+              p->termination_tol, p->mu_dynamic, p->use_filter_line_search, p->filter_size};
+  mimgpu_sqp_params dp{reg0, reg0, p->mu_dynamic, 0, 0};
+  /* per-problem regularisation and cost live in the solve state */
+  const double* save_cost = c->k.cost;
+  c->k.cost = s.cost;
+  c->k.preg_arr = s.preg;
+  c->k.dreg_arr = s.dreg;
+  int32_t counts[4];
+  auto read_counts = [&]() -> int {
+    CU(cudaMemcpyAsync(counts, s.counts, sizeof(counts), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    return MIMGPU_OK;
+  };
+  auto kerr = [&](const char* what) -> int {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(MIMGPU_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+    c->launches++;
+    return MIMGPU_OK;
+  };
+  /* one pass of "computeDirection with the regularisation retry + KKT test" on the running problems
+   * (list_a, n_run of them); leaves the line-search candidates in list_b, their number in counts[1] */
+  auto direction_pass = [&](int n_run) -> int {
+    if (solve_calcdiff_launch_x(c->k, c->model, s, s.list_a, n_run, st) != 0)
+      return fail(MIMGPU_ERR_UNSUPPORTED, "model kernels: shape needs more than 48 KB of shared memory");
+    if ((rc = kerr("k_model_calcdiff"))) return rc;
+    c->pack_dirty = true;
+    CU(cudaMemsetAsync(s.counts, 0, 2 * sizeof(int32_t), st));
+    int n_dir = n_run;
+    int n_ls = 0;
+    int32_t *cur = s.list_a, *nxt = s.flag;   /* the retry list ping-pongs between two buffers */
+    while (n_dir > 0) {
+      c->k.active = cur; c->k.n_active = n_dir;
+      rc = mimgpu_sqp_direction(c, &dp, st);
+      if (rc) return rc;
+      solve_post_direction_launch_x(c->k, s, sp, cur, n_dir, nxt, st);
+      if ((rc = kerr("k_sqp_post_direction"))) return rc;
+      if ((rc = read_counts())) return rc;
+      n_ls = counts[1];
+      n_dir = counts[0];                        /* problems whose backward pass failed: again, with more regularisation */
+      if (n_dir > 0) CU(cudaMemsetAsync(s.counts, 0, sizeof(int32_t), st));
+      std::swap(cur, nxt);
+    }
+    counts[1] = n_ls;
+    return MIMGPU_OK;
+  };
+  auto running = [&](int* n_run) -> int {
+    CU(cudaMemsetAsync(s.counts + 2, 0, sizeof(int32_t), st));
+    solve_running_launch_x(s, B, st);
+    if ((rc = kerr("k_solve_running"))) return rc;
+    if ((rc = read_counts())) return rc;
+    *n_run = counts[2];
+    return MIMGPU_OK;
+  };
+  int n_run = 0, it = 0;
+  rc = running(&n_run);
+  for (; rc == MIMGPU_OK && it < p->maxiter && n_run > 0; ++it) {
+    if ((rc = direction_pass(n_run))) break;
+    if (counts[1] > 0) {
+      if (solve_linesearch_launch_x(c->k, c->model, s, sp, s.list_b, counts[1], st) != 0) {
+        rc = fail(MIMGPU_ERR_UNSUPPORTED, "line-search kernel: shape needs more than 48 KB of shared memory");
+        break;
+      }
+      if ((rc = kerr("k_sqp_linesearch"))) break;
+    }
+    if ((rc = running(&n_run))) break;
+  }
+  if (rc == MIMGPU_OK && p->extra_iteration_for_last_kkt && n_run > 0) rc = direction_pass(n_run);
+  c->k.active = nullptr; c->k.n_active = B;
+  c->k.cost = s.cost; (void)save_cost;
+  c->last_stream = st;
+  if (n_sqp_iters) *n_sqp_iters = it;
+  return rc;
+}
+
+int mimgpu_solve_info(mimgpu_ctx* c, int32_t* iters, int32_t* outcome, void* stream) {
+  if (!c) return fail(MIMGPU_ERR_INVALID, "null pointer");
+  if (!c->solve_buf) return fail(MIMGPU_ERR_STATE, "no mimgpu_sqp_solve has run on this ctx");
+  CU(cudaSetDevice(c->device));
+  const size_t B = c->sh.B;
+  if (iters) CU(cudaMemcpyAsync(iters, c->sv.iter, B * sizeof(int32_t), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  if (outcome) CU(cudaMemcpyAsync(outcome, c->sv.done, B * sizeof(int32_t), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  CU(cudaStreamSynchronize((cudaStream_t)stream));
+  return MIMGPU_OK;
+}
+
 /* ----------------------------------------------------------------- data out */
 /* Qu_, Quuk_ and Quu_llt_ are solver members the reference keeps per knot but that neither the
  * SQP forward pass nor its outputs use; the fast small-shape kernel does not spill them.  When
@@ -820,7 +1013,9 @@ static int refresh_extras(mimgpu_ctx* c, int field, cudaStream_t st) {
   int rc0 = ensure_fields(c, st);
   if (rc0) return rc0;
   if (c->k.n_active > 0) {
-    if (small_sqp_direction_launch_x(c->k, c->last_sqp, 1, st) != 1)
+    KArgs ka = c->k;
+    ka.pad_ = 1; /* members only: dx_ / du_ / lag_mul_ / scalars / status of the fast launch are left alone */
+    if (small_sqp_direction_launch_x(ka, c->last_sqp, 1, st) != 1)
       return fail(MIMGPU_ERR_CUDA, "full-spill kernel launch failed");
     int rc = post_launch(c, "k_sqp_direction_small");
     if (rc) return rc;

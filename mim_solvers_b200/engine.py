@@ -119,6 +119,46 @@ class BatchEngine:
                                                           ptr(du), ptr(lag_mul), ptr(kkt), int(n_chunks)),
               "mimgpu_sqp_direction_host_records")
 
+    # ---- solve() on the device (analytic models) -----------------------------------
+    def attach_model(self, arrays: dict, c3: float = 0.0, w4: float = 0.0):
+        """mimgpu_model_attach: `arrays` maps A Bm f Q S R q r QT qT x0 to float64 arrays in the C-ABI block
+        layouts (numpy: copied to the device; torch CUDA tensors: attached)."""
+        m = _capi.PolyModel()
+        m.c3, m.w4 = float(c3), float(w4)
+        dev = all(hasattr(v, "data_ptr") for v in arrays.values())
+        keep = {}
+        for n in ("A", "Bm", "f", "Q", "S", "R", "q", "r", "QT", "qT", "x0"):
+            v = arrays[n]
+            if dev:
+                assert v.is_cuda and v.is_contiguous()
+                setattr(m, n, v.data_ptr() if v.numel() else None)
+            else:
+                v = np.ascontiguousarray(v, dtype=np.float64)
+                setattr(m, n, v.ctypes.data if v.size else None)
+            keep[n] = v
+        self._keep_model = keep
+        check(self._lib.mimgpu_model_attach(self._ctx, C.byref(m), _capi.MEM_DEVICE if dev else _capi.MEM_HOST,
+                                            self.stream), "mimgpu_model_attach")
+        self.sync()
+
+    def sqp_solve(self, params=None, xs0=None, us0=None) -> int:
+        """mimgpu_sqp_solve: SolverSQP::solve for all problems on the device; returns the number of SQP
+        iterations of the slowest problem."""
+        p = params or _capi.default_sqp_solve_params()
+        x = None if xs0 is None else np.ascontiguousarray(xs0, dtype=np.float64)
+        u = None if us0 is None else np.ascontiguousarray(us0, dtype=np.float64)
+        n = C.c_int32(0)
+        check(self._lib.mimgpu_sqp_solve(self._ctx, C.byref(p), _capi.as_ptr(x), _capi.as_ptr(u), C.byref(n),
+                                         self.stream), "mimgpu_sqp_solve")
+        return int(n.value)
+
+    def solve_info(self):
+        """(iter_ [B], outcome [B]: 1 converged, 2 stopped at the regularisation limit, 0 maxiter)."""
+        B = self._shape.B
+        it, oc = np.empty(B, dtype=np.int32), np.empty(B, dtype=np.int32)
+        check(self._lib.mimgpu_solve_info(self._ctx, it.ctypes.data, oc.ctypes.data, self.stream), "mimgpu_solve_info")
+        return it, oc
+
     def set_reg(self, preg=None, dreg=None):
         p = None if preg is None else np.ascontiguousarray(preg, dtype=np.float64)
         d = None if dreg is None else np.ascontiguousarray(dreg, dtype=np.float64)

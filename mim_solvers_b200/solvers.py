@@ -120,6 +120,50 @@ class LQBatchProblem(BatchShootingProblem):
         return b
 
 
+class PolyBatchProblem(LQBatchProblem):
+    """LQ plus separable polynomial terms -- the analytic model family the device-side solve()
+    evaluates (include/mimgpu.h, mimgpu_poly_model):
+      x+ = A x + B u + f + c3 x^3,   l_t += w4/4 sum x_i^4,   l_T += w4/4 sum x_i^4.
+    c3 = w4 = 0 is LQBatchProblem.  Unconstrained (ng = ngT = 0)."""
+
+    def __init__(self, x0, A, Bm, f, Q, S, R, q, r, QT, qT, c3=0.0, w4=0.0):
+        super().__init__(x0, A, Bm, f, Q, S, R, q, r, QT, qT)
+        self.c3, self.w4 = float(c3), float(w4)
+
+    def calc(self, xs, us):
+        out = super().calc(xs, us)
+        x = xs[:, :-1]
+        out["xnext"] = out["xnext"] + self.c3 * x**3
+        out["cost"] = out["cost"] + 0.25 * self.w4 * ((x**4).sum(axis=(1, 2)) + (xs[:, -1]**4).sum(axis=1))
+        return out
+
+    def calc_knot(self, t, x, u):
+        xn, c = super().calc_knot(t, x, u)
+        return xn + self.c3 * x**3, c + 0.25 * self.w4 * (x**4).sum(axis=1)
+
+    def calc_terminal(self, x):
+        return super().calc_terminal(x) + 0.25 * self.w4 * (x**4).sum(axis=1)
+
+    def calcDiff(self, xs, us):
+        b = super().calcDiff(xs, us)
+        x, xT = xs[:, :-1], xs[:, -1]
+        eye = np.eye(self.nx)
+        b.set("Fx", self.A + 3.0 * self.c3 * (x**2)[..., None] * eye)
+        b.set("Lxx", self.Q + 3.0 * self.w4 * (x**2)[..., None] * eye)
+        b.set("Lx", b.arrays["Lx"] + self.w4 * x**3)
+        b.set("LxxT", self.QT + 3.0 * self.w4 * (xT**2)[..., None] * eye)
+        b.set("LxT", b.arrays["LxT"] + self.w4 * xT**3)
+        return b
+
+    def model_arrays(self) -> dict:
+        """The model in the block layouts of the C ABI (column-major blocks)."""
+        from .problems import to_colmajor
+        return dict(A=to_colmajor(self.A), Bm=to_colmajor(self.Bm), f=np.ascontiguousarray(self.f),
+                    Q=to_colmajor(self.Q), S=to_colmajor(self.S), R=to_colmajor(self.R),
+                    q=np.ascontiguousarray(self.q), r=np.ascontiguousarray(self.r), QT=to_colmajor(self.QT),
+                    qT=np.ascontiguousarray(self.qT), x0=np.ascontiguousarray(self.x0))
+
+
 def _default_engine_factory(batch: OCPBatch):
     from .engine import BatchEngine  # CUDA only; raises without libmimgpu.so / a device
     return BatchEngine(batch)
@@ -420,6 +464,39 @@ class SolverSQP(_SolverBase):
             running &= ~gave_up
             converged |= running & (self.KKT <= self.termination_tolerance)
         return converged
+
+
+    def solve_on_device(self, init_xs=None, init_us=None, maxiter=100, is_feasible=False, reginit=float("nan"),
+                        device=0):
+        """The same solve(), with the whole loop on the GPU (mimgpu_sqp_solve): model calc / calcDiff,
+        computeDirection, KKT test, filter / merit line search and the regularisation schedule run there for
+        every problem; nothing but two counters per iteration crosses PCIe.  Needs a PolyBatchProblem (an
+        analytic model the device can evaluate).  Returns converged [B]."""
+        from .engine import BatchEngine
+        p = self.problem
+        if not isinstance(p, PolyBatchProblem):
+            raise TypeError("solve_on_device needs an analytic model (PolyBatchProblem)")
+        if getattr(self, "_dev_engine", None) is None:
+            shape = _capi.Shape(p.B, p.T, p.nx, p.nu, 0, 0)
+            self._dev_engine = BatchEngine(shape=shape, device=device)
+            self._dev_engine.attach_model(p.model_arrays(), p.c3, p.w4)
+        e = self._dev_engine
+        sp = _capi.default_sqp_solve_params(
+            maxiter=maxiter, use_filter_line_search=int(self.use_filter_line_search), filter_size=self.filter_size,
+            extra_iteration_for_last_kkt=int(self.extra_iteration_for_last_kkt), reg_init=reginit,
+            reg_min=self.reg_min, reg_max=self.reg_max, reg_incfactor=self.reg_incFactor,
+            reg_decfactor=self.reg_decFactor, th_stepdec=self.th_stepDec, th_stepinc=self.th_stepInc,
+            termination_tol=self.termination_tolerance, mu_dynamic=self.mu_dynamic)
+        self.n_device_iters = e.sqp_solve(sp, init_xs, init_us)
+        self.xs, self.us = e.field("xs"), e.field("us")
+        it, outcome = e.solve_info()
+        self.iter[:] = it
+        for name, attr in (("KKT", "KKT"), ("cost", "cost"), ("gap_norm", "gap_norm"), ("merit", "merit"),
+                           ("steplength", "steplength"), ("preg", "preg"), ("preg", "dreg"),
+                           ("x_grad_norm", "x_grad_norm"), ("u_grad_norm", "u_grad_norm")):
+            getattr(self, attr)[:] = e.scalar(name)
+        self._engine = e
+        return outcome == 1
 
 
 # ------------------------------------------------------------------------------ SolverFDDP

@@ -206,8 +206,12 @@ def test_gpu_knot_records_layout(eng, oracle_lib):
     batch = make_random_batch(37, 20, 12, 6)
     a = eng(batch)
     a.sqp_direction()
+    kkt, st0 = a.scalar("KKT"), a.status.copy()
     ref = {n: a.field(n) for n in ("dx", "du", "lag_mul", "K", "Vxx", "Qu", "Quu_llt")}
-    kkt = a.scalar("KKT")
+    # asking for Qu_ / Quu_llt_ reruns the full-spill kernel for the members only: the direction, the
+    # scalars and the status of the fast launch are not rewritten
+    assert np.array_equal(a.scalar("KKT"), kkt) and np.array_equal(a.status, st0)
+    assert np.array_equal(a.field("dx"), ref["dx"])
     b = eng(shape=batch.shape())
     L = b.record_layout()
     assert L.problem_doubles == batch.T * L.rec_doubles + L.term_doubles
