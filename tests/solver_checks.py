@@ -105,3 +105,58 @@ def check_fddp_lq(factory):
     ref = SolverSQP(p, factory)
     ref.solve(maxiter=10)
     assert np.abs(ref.us - s.us).max() < 1e-5
+
+
+# ------------------------------------------------------------------ multi-iteration goldens
+GOLDEN_SOLVE = ("solve_lq", "solve_poly_filter", "solve_poly_filter3", "solve_poly_short_steps", "solve_poly_merit",
+                "solve_poly_merit2")
+
+
+def load_solve_golden(name):
+    """Fixtures recorded from the reference's own python/sqp.py SQP.solve() (tests/golden/make_golden_solve.py)."""
+    from pathlib import Path
+    from mim_solvers_b200.solvers import PolyBatchProblem
+    z = np.load(Path(__file__).resolve().parent / "golden" / f"{name}.npz")
+    p = PolyBatchProblem(z["x0"], z["A"], z["Bm"], z["f"], z["Q"], z["S"], z["R"], z["q"], z["r"], z["QT"], z["qT"],
+                         c3=float(z["c3"]), w4=float(z["w4"]))
+    return p, z
+
+
+def check_solve_golden(name, factory=None, device=False, tol=1e-8):
+    """Replay one multi-iteration fixture through the batched SolverSQP (host loop, or the loop on the
+    device): identical iteration counts and outcome, the accepted step length of every iteration, final
+    xs / us / KKT.  The NumPy reference has no regularisation: reg_min = reginit = 0."""
+    p, z = load_solve_golden(name)
+    s = SolverSQP(p, factory)
+    s.use_filter_line_search = bool(z["use_filter"])
+    s.filter_size = int(z["filter_size"])
+    s.reg_min = 0.0
+    maxiter = int(z["maxiter"])
+    xs0 = np.repeat(p.x0[:, None, :], p.T + 1, axis=1)
+    us0 = np.zeros((p.B, p.T, p.nu))
+    steps = []
+    if device:
+        ok = s.solve_on_device(xs0, us0, maxiter=maxiter, reginit=0.0)
+    else:
+        prev = {"xs": xs0.copy()}
+
+        def cb(sol, _name):   # called after every computeDirection: which step did the previous search take?
+            steps.append(sol.steplength.copy())
+        s.setCallbacks([cb])
+        ok = s.solve(xs0, us0, maxiter=maxiter, reginit=0.0)
+        del prev
+    assert np.array_equal(ok.astype(int), z["out_converged"]), (name, ok, z["out_converged"])
+    assert np.array_equal(s.iter, z["out_iter"]), (name, s.iter, z["out_iter"])
+    for got, ref, what in ((s.xs, z["out_xs"], "xs"), (s.us, z["out_us"], "us")):
+        err = np.abs(got - ref).reshape(p.B, -1).max(axis=1) / np.abs(ref).reshape(p.B, -1).max(axis=1)
+        assert err.max() <= tol, (name, what, err)
+    conv = z["out_converged"].astype(bool)
+    assert np.all(np.abs(s.KKT - z["out_KKT"])[conv] <= tol * np.maximum(1.0, z["out_KKT"][conv]))
+    if not device and len(steps) > 1:
+        # steps[k] (k >= 1) holds, for the problems still running, the step accepted by line search k - 1
+        ref_a = 2.0 ** np.round(np.log2(z["out_alphas"]))   # recorded as a ratio: snap to the 2^-n grid
+        for b in range(p.B):
+            n = int(np.isfinite(ref_a[b]).sum())
+            mine = [steps[k][b] for k in range(1, min(len(steps), n + 1))]
+            assert np.array_equal(np.array(mine), ref_a[b, :len(mine)]), (name, b, mine, ref_a[b, :n])
+    return s

@@ -86,3 +86,11 @@ def test_device_solve_large_batch_lq():
     assert ok.all() and (s.iter == 1).all()
     c = p.calc(s.xs, s.us)
     assert np.abs(c["xnext"] - s.xs[:, 1:]).max() < 1e-9
+
+
+@pytest.mark.parametrize("device", [False, True], ids=["host-loop", "device-loop"])
+@pytest.mark.parametrize("name", sc.GOLDEN_SOLVE)
+def test_solve_against_reference_python_solve(name, device):
+    """Multi-iteration fixtures recorded from the reference's python/sqp.py SQP.solve(): iteration counts,
+    outcome, accepted step lengths, final xs / us / KKT, through the host loop and through the device loop."""
+    sc.check_solve_golden(name, None, device=device)

@@ -25,6 +25,13 @@ def test_solver_host(factory, check):
     check(factory)
 
 
+@pytest.mark.parametrize("name", sc.GOLDEN_SOLVE)
+def test_solve_loop_against_reference_python_solve(factory, name):
+    """Row a15: the solve() loop (filter / merit acceptance, alpha < 1, iteration counts) against fixtures
+    recorded from the reference's own NumPy SQP.solve() -- not against itself."""
+    sc.check_solve_golden(name, factory)
+
+
 def test_default_engine_is_cuda_only():
     """No CPU fallback: without a device the default engine factory raises."""
     import ctypes
