@@ -247,6 +247,64 @@ class LQBatchProblem : public BatchShootingProblem {
   }
 };
 
+/* LQ plus separable polynomial terms -- the analytic model family the DEVICE-side solve() evaluates
+ * (include/mimgpu.h, mimgpu_poly_model):  x+ = A x + B u + f + c3 x^3,  l_t += w4/4 sum x_i^4,
+ * l_T += w4/4 sum x_i^4.  c3 = w4 = 0 is LQBatchProblem.  Unconstrained. */
+class PolyBatchProblem : public LQBatchProblem {
+ public:
+  double c3 = 0.0, w4 = 0.0;
+
+  double calcKnot(int b, int t, const double* x, const double* u, double* xnext) override {
+    double c = LQBatchProblem::calcKnot(b, t, x, u, xnext);
+    for (int i = 0; i < sh.nx; ++i) { const double x2 = x[i] * x[i]; xnext[i] += c3 * x2 * x[i]; c += 0.25 * w4 * x2 * x2; }
+    return c;
+  }
+  double calcTerminal(int b, const double* x) override {
+    double c = LQBatchProblem::calcTerminal(b, x);
+    for (int i = 0; i < sh.nx; ++i) { const double x2 = x[i] * x[i]; c += 0.25 * w4 * x2 * x2; }
+    return c;
+  }
+  double calc(int b, const double* xs, const double* us, double* xnext, double* g, double* gT) override {
+    const int T = sh.T, nx = sh.nx, nu = sh.nu;
+    double c = 0.0;
+    for (int t = 0; t < T; ++t) c += calcKnot(b, t, xs + (size_t)t * nx, us + (size_t)t * nu, xnext + (size_t)t * nx);
+    (void)g; (void)gT;
+    return c + calcTerminal(b, xs + (size_t)T * nx);
+  }
+  void calcDiff(int b, const double* xs, const double* us, const KnotDerivs& d) override {
+    LQBatchProblem::calcDiff(b, xs, us, d);
+    const int T = sh.T, nx = sh.nx;
+    for (int t = 0; t <= T; ++t) {
+      const double* x = xs + (size_t)t * nx;
+      for (int i = 0; i < nx; ++i) {
+        const double x2 = x[i] * x[i];
+        if (t < T) {
+          d.Fx[(size_t)t * nx * nx + i + nx * i] += 3.0 * c3 * x2;
+          d.Lxx[(size_t)t * nx * nx + i + nx * i] += 3.0 * w4 * x2;
+          d.Lx[(size_t)t * nx + i] += w4 * x2 * x[i];
+        } else {
+          d.LxxT[i + nx * i] += 3.0 * w4 * x2;
+          d.LxT[i] += w4 * x2 * x[i];
+        }
+      }
+    }
+  }
+  /* the model in the column-major block layouts of the C ABI */
+  struct AbiArrays { Vec A, Bm, Q, S, R, QT; };
+  AbiArrays abi() const {
+    const size_t B = sh.B, T = sh.T, nx = sh.nx, nu = sh.nu;
+    auto tr = [](const Vec& src, size_t nblk, size_t r, size_t c) { /* row-major r x c -> col-major */
+      Vec o(src.size());
+      for (size_t k = 0; k < nblk; ++k)
+        for (size_t i = 0; i < r; ++i)
+          for (size_t j = 0; j < c; ++j) o[k * r * c + i + r * j] = src[k * r * c + i * c + j];
+      return o;
+    };
+    return AbiArrays{tr(A, B * T, nx, nx), tr(Bm, B * T, nx, nu), tr(Q, B * T, nx, nx), tr(S, B * T, nx, nu),
+                     tr(R, B * T, nu, nu), tr(QT, B, nx, nx)};
+  }
+};
+
 /* ------------------------------------------------------------------ RAII handle of one mimgpu_ctx */
 class Engine {
  public:
@@ -259,6 +317,16 @@ class Engine {
 
   const mimgpu_shape& shape() const { return sh_; }
   mimgpu_ctx* ctx() const { return ctx_; }
+  void model_attach(const mimgpu_poly_model& m) { check(mimgpu_model_attach(ctx_, &m, MIMGPU_MEM_HOST, stream_), "mimgpu_model_attach"); sync(); }
+  int sqp_solve(const mimgpu_sqp_solve_params& p, const double* xs0, const double* us0) {
+    int32_t n = 0;
+    check(mimgpu_sqp_solve(ctx_, &p, xs0, us0, &n, stream_), "mimgpu_sqp_solve");
+    return n;
+  }
+  void solve_info(std::vector<int32_t>& iters, std::vector<int32_t>& outcome) {
+    iters.resize(sh_.B); outcome.resize(sh_.B);
+    check(mimgpu_solve_info(ctx_, iters.data(), outcome.data(), stream_), "mimgpu_solve_info");
+  }
   void sync() { check(mimgpu_stream_sync(ctx_, stream_), "mimgpu_stream_sync"); }
   void upload(const HostDerivs& d) {
     mimgpu_derivs v = d.c_view();
@@ -284,8 +352,8 @@ class Engine {
   size_t field_size(int field) const {
     const size_t B = sh_.B, T = sh_.T, nx = sh_.nx, nu = sh_.nu, nc = T * sh_.ng + sh_.ngT;
     switch (field) {
-      case MIMGPU_F_DX: case MIMGPU_F_LAG_MUL: case MIMGPU_F_DX_TILDE: case MIMGPU_F_VX: return B * (T + 1) * nx;
-      case MIMGPU_F_DU: case MIMGPU_F_DU_TILDE: case MIMGPU_F_KFF: case MIMGPU_F_QU: case MIMGPU_F_QUUK: return B * T * nu;
+      case MIMGPU_F_DX: case MIMGPU_F_LAG_MUL: case MIMGPU_F_DX_TILDE: case MIMGPU_F_VX: case MIMGPU_F_XS: return B * (T + 1) * nx;
+      case MIMGPU_F_DU: case MIMGPU_F_DU_TILDE: case MIMGPU_F_KFF: case MIMGPU_F_QU: case MIMGPU_F_QUUK: case MIMGPU_F_US: return B * T * nu;
       case MIMGPU_F_Y: case MIMGPU_F_Z: case MIMGPU_F_RHO_VEC: return B * nc;
       case MIMGPU_F_VXX: return B * (T + 1) * nx * nx;
       case MIMGPU_F_K: return B * T * nu * nx;
@@ -395,6 +463,7 @@ class BatchSolverBase {
 
   /* ---- accessors (names of bindings/ddp.cpp:63-238, bindings/sqp.cpp:41-117) */
   const mimgpu_shape& shape() const { return sh_; }
+  std::shared_ptr<BatchShootingProblem> problem() const { return problem_; }
   const Vec& get_xs() const { return xs_; }
   const Vec& get_us() const { return us_; }
   const Vec& get_xs_try() const { return xs_try_; }
@@ -650,7 +719,57 @@ class BatchSolverSQP : public BatchSolverBase {
   const Vec& get_xgrad_norm() const { return x_grad_norm_; }
   const Vec& get_ugrad_norm() const { return u_grad_norm_; }
 
+  /* The same solve() with the WHOLE loop on the GPU (mimgpu_sqp_solve): model calc / calcDiff,
+   * computeDirection, KKT test, line search, acceptance and regularisation schedule per problem; needs an
+   * analytic model the device can evaluate (PolyBatchProblem).  Throws std::invalid_argument otherwise. */
+  std::vector<bool> solveOnDevice(const Vec& init_xs = Vec(), const Vec& init_us = Vec(), size_t maxiter = 100,
+                                  bool /*is_feasible*/ = false, double reginit = NAN) {
+    auto* pm = dynamic_cast<PolyBatchProblem*>(problem_.get());
+    if (!pm) throw std::invalid_argument("Invalid argument: solveOnDevice needs an analytic model (PolyBatchProblem)");
+    if (sh_.ng || sh_.ngT) throw std::invalid_argument("Invalid argument: solveOnDevice handles unconstrained problems");
+    const size_t B = sh_.B;
+    if (!init_xs.empty() && init_xs.size() != xs_.size()) throw std::invalid_argument("Invalid argument: xs has wrong dimension");
+    if (!init_us.empty() && init_us.size() != us_.size()) throw std::invalid_argument("Invalid argument: us has wrong dimension");
+    if (!engine_) engine_ = std::make_unique<Engine>(sh_, device_);
+    if (!model_attached_) {
+      const PolyBatchProblem::AbiArrays a = pm->abi();
+      mimgpu_poly_model m;
+      m.A = a.A.data(); m.Bm = a.Bm.data(); m.f = pm->f.data(); m.Q = a.Q.data(); m.S = a.S.data(); m.R = a.R.data();
+      m.q = pm->q.data(); m.r = pm->r.data(); m.QT = a.QT.data(); m.qT = pm->qT.data(); m.x0 = pm->X0.data();
+      m.c3 = pm->c3; m.w4 = pm->w4;
+      engine_->model_attach(m);
+      model_attached_ = true;
+    }
+    mimgpu_sqp_solve_params sp;
+    sp.maxiter = (int32_t)maxiter; sp.use_filter_line_search = use_filter_line_search_; sp.filter_size = filter_size_;
+    sp.extra_iteration_for_last_kkt = extra_iteration_for_last_kkt_; sp.reg_init = reginit; sp.reg_min = reg_min_;
+    sp.reg_max = reg_max_; sp.reg_incfactor = reg_incfactor_; sp.reg_decfactor = reg_decfactor_;
+    sp.th_stepdec = th_stepdec_; sp.th_stepinc = th_stepinc_; sp.termination_tol = termination_tol_; sp.mu_dynamic = mu_dynamic_;
+    /* crocoddyl's setCandidate: empty warm start = x0 at every knot here (as setCandidate above), zero controls */
+    Vec xs0 = init_xs;
+    if (xs0.empty()) {
+      xs0.resize(xs_.size());
+      for (size_t b = 0; b < B; ++b)
+        for (int t = 0; t <= sh_.T; ++t) std::memcpy(&xs0[xoff((int)b, t)], pm->x0((int)b), sh_.nx * sizeof(double));
+    }
+    n_device_passes_ = engine_->sqp_solve(sp, xs0.data(), init_us.empty() ? nullptr : init_us.data());
+    xs_ = engine_->field(MIMGPU_F_XS); us_ = engine_->field(MIMGPU_F_US);
+    std::vector<int32_t> it, oc;
+    engine_->solve_info(it, oc);
+    const Mask all(B, 1);
+    pull(MIMGPU_S_KKT, KKT_, all); pull(MIMGPU_S_COST, cost_, all); pull(MIMGPU_S_GAP_NORM, gap_norm_, all);
+    pull(MIMGPU_S_MERIT, merit_, all); pull(MIMGPU_S_STEPLENGTH, steplength_, all); pull(MIMGPU_S_PREG, preg_, all);
+    pull(MIMGPU_S_XGRAD_NORM, x_grad_norm_, all); pull(MIMGPU_S_UGRAD_NORM, u_grad_norm_, all);
+    dreg_ = preg_;
+    std::vector<bool> converged(B);
+    for (size_t b = 0; b < B; ++b) { iter_[b] = it[b]; converged[b] = (oc[b] == 1); }
+    return converged;
+  }
+  int get_device_passes() const { return n_device_passes_; }
+
  private:
+  bool model_attached_ = false;
+  int n_device_passes_ = 0;
   void launchDirection() {
     mimgpu_sqp_params p;
     p.preg = reg_min_; p.dreg = reg_min_; p.mu_dynamic = mu_dynamic_; p.is_feasible = 0; p.reserved = 0;
