@@ -396,16 +396,10 @@ def run_workload(args, name, rank, world, local_rank, *, steps, warmup, e2e_step
                 eng2.sqp_direction_host(pinned, p, dx=outs["dx"].numpy(), du=outs["du"].numpy(),
                                         lag_mul=outs["lag_mul"].numpy(), kkt=kkt.numpy(), n_chunks=args.e2e_chunks)
                 return
-            eng2.upload(pinned)
-            eng2.csqp_calc_norms()
-            eng2.csqp_reset_rho(p)
-            eng2.csqp_direction(p, with_kkt=True)
-            for n, t in outs.items():
-                if t.numel():
-                    eng2.download_into(n, t.numpy())
-            _capi.check(eng2._lib.mimgpu_scalar(eng2._ctx, _capi.SCALARS["KKT"], kkt.numpy().ctypes.data,
-                                               eng2.stream), "mimgpu_scalar")
-            eng2.sync()
+            on = lambda k: outs[k].numpy() if outs[k].numel() else None
+            eng2.csqp_direction_host(pinned, p, with_kkt=True, calc_norms=True, reset_rho=True,
+                                     dx_tilde=on("dx_tilde"), du_tilde=on("du_tilde"), lag_mul=on("lag_mul"),
+                                     y=on("y"), z=on("z"), kkt=kkt.numpy(), n_chunks=args.e2e_chunks)
 
         for _ in range(2):
             e2e_step()
@@ -420,7 +414,7 @@ def run_workload(args, name, rank, world, local_rank, *, steps, warmup, e2e_step
                "h2d_gbs_per_rank": h2d / dt / 1e9,
                "call": ("mimgpu_sqp_direction_host_records" if use_rec else "mimgpu_sqp_direction_host")
                        + " (%d overlapped slices)" % args.e2e_chunks if solver == "sqp"
-                       else "mimgpu_upload + csqp_direction + mimgpu_download",
+                       else "mimgpu_csqp_direction_host (%d overlapped slices)" % args.e2e_chunks,
                "max_kkt": float(kkt.max())}
         eng2.close()
         torch.cuda.empty_cache()

@@ -302,6 +302,15 @@ int mimgpu_csqp_reset_rho(mimgpu_ctx* ctx, const mimgpu_csqp_params* p,
 int mimgpu_csqp_direction(mimgpu_ctx* ctx, const mimgpu_csqp_params* p,
                           int with_kkt, void* cuda_stream);
 
+/* The same computeDirection for HOST-resident derivatives, end to end: upload, (optionally) calc norms and
+ * rho reset, the ADMM loop and the download of dx~ / du~ / lag_mul / y / z [B][..], KKT [B] and qp_iters [B]
+ * (any of them may be NULL) in `n_chunks` slices of the batch on two internal streams, so that the PCIe
+ * copies overlap the kernels.  Synchronous; pin the host memory. */
+int mimgpu_csqp_direction_host(mimgpu_ctx* ctx, const mimgpu_derivs* host_derivs, const mimgpu_csqp_params* p,
+                               int with_kkt, int calc_norms, int reset_rho, double* dx_tilde, double* du_tilde,
+                               double* lag_mul, double* y, double* z, double* kkt, int32_t* qp_iters,
+                               int32_t n_chunks);
+
 /* ---- solve() on the device (analytic models) -------------------------------- */
 /* For problems whose running / terminal models can be evaluated on the GPU the whole
  * SolverSQP::solve (src/sqp.cpp:75-222) runs there: model calc / calcDiff, computeDirection,

@@ -141,7 +141,7 @@ SYMBOLS = (
     "mimgpu_set_active", "mimgpu_set_field", "mimgpu_sqp_direction",
     "mimgpu_sqp_direction_host", "mimgpu_sqp_direction_host_records", "mimgpu_get_record_layout",
     "mimgpu_upload_records", "mimgpu_model_attach", "mimgpu_sqp_solve", "mimgpu_solve_info", "mimgpu_fddp_direction", "mimgpu_csqp_calc_norms", "mimgpu_csqp_reset_rho",
-    "mimgpu_csqp_direction", "mimgpu_download", "mimgpu_field_ptr", "mimgpu_scalar",
+    "mimgpu_csqp_direction", "mimgpu_csqp_direction_host", "mimgpu_download", "mimgpu_field_ptr", "mimgpu_scalar",
     "mimgpu_iters_status", "mimgpu_converged", "mimgpu_summary_reduce", "mimgpu_launch_count", "mimgpu_stream_sync", "mimgpu_measure_peaks",
 )
 
@@ -173,6 +173,8 @@ def _declare(lib):
     lib.mimgpu_csqp_calc_norms.argtypes = [vp, vp]
     lib.mimgpu_csqp_reset_rho.argtypes = [vp, C.POINTER(CsqpParams), vp]
     lib.mimgpu_csqp_direction.argtypes = [vp, C.POINTER(CsqpParams), C.c_int, vp]
+    lib.mimgpu_csqp_direction_host.argtypes = [vp, C.POINTER(Derivs), C.POINTER(CsqpParams), C.c_int, C.c_int, C.c_int,
+                                               vp, vp, vp, vp, vp, vp, vp, i32]
     lib.mimgpu_download.argtypes = [vp, C.c_int, vp, vp]
     lib.mimgpu_field_ptr.argtypes = [vp, C.c_int, C.POINTER(vp), C.POINTER(i64), vp]
     lib.mimgpu_scalar.argtypes = [vp, C.c_int, vp, vp]

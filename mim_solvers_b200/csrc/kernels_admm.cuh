@@ -839,7 +839,7 @@ k_csqp_direction_admm(KArgs a, AdmmKPar kp) {
   static_assert(NX % 2 == 0 && NU % 2 == 0 && NU <= 32, "16-byte rows, one lane per control in the gain solve");
   extern __shared__ __align__(16) double sm_admm[];
   if ((int)blockIdx.x >= a.n_active) return;
-  const int b = a.active ? a.active[blockIdx.x] : (int)blockIdx.x;
+  const int b = a.active ? a.active[blockIdx.x] : (int)blockIdx.x + a.first;
   Prob p = bind(a, b);
   const int nw = blockDim.x >> 5;
   constexpr bool STAGED = admm_staged<NX, NU>();

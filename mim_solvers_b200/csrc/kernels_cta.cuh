@@ -63,7 +63,7 @@ k_csqp_direction_stream(KArgs a, StreamKPar kp) {
   static_assert(NX % 2 == 0 && NU % 2 == 0, "TMA bulk copies need 16-byte blocks");
   extern __shared__ __align__(16) double sm_stream[];
   if ((int)blockIdx.x >= a.n_active) return;
-  const int b = a.active ? a.active[blockIdx.x] : (int)blockIdx.x;
+  const int b = a.active ? a.active[blockIdx.x] : (int)blockIdx.x + a.first;
   Prob p = bind(a, b);
   const StreamSmem ss = stream_layout<NX, NU>(p.ng, p.ngT, kp.ns, kp.generic_total);
   double* sm = sm_stream;
@@ -278,7 +278,7 @@ template <int NX, int NU, bool FDDP>
 __global__ void __launch_bounds__(CtaTune<NX, NU>::MAXT, CtaTune<NX, NU>::MINB) k_sqp_direction_cta(KArgs a, SqpKPar kp, int nbuf, int ns) {
   extern __shared__ __align__(16) double sm_cta[];
   if ((int)blockIdx.x >= a.n_active) return;
-  const int b = a.active ? a.active[blockIdx.x] : (int)blockIdx.x;
+  const int b = a.active ? a.active[blockIdx.x] : (int)blockIdx.x + a.first;
   Prob p = bind(a, b);
   uint64_t* bars = reinterpret_cast<uint64_t*>(sm_cta); /* [0,1]: backward sweep, [2..5): forward pipeline */
   double* um = sm_cta + 8;

@@ -147,30 +147,30 @@ static void field_sizes(const mimgpu_shape& s, size_t n[MIMGPU_F_COUNT]) {
 __global__ void __launch_bounds__(512) k_sqp_direction_generic(KArgs a, SqpKPar kp) {
   extern __shared__ double sm[];
   if ((int)blockIdx.x >= a.n_active) return;
-  const int b = a.active ? a.active[blockIdx.x] : (int)blockIdx.x;
+  const int b = a.active ? a.active[blockIdx.x] : (int)blockIdx.x + a.first;
   sqp_direction_body(a, b, sm, kp);
 }
 __global__ void __launch_bounds__(512) k_fddp_direction_generic(KArgs a, SqpKPar kp) {
   extern __shared__ double sm[];
   if ((int)blockIdx.x >= a.n_active) return;
-  const int b = a.active ? a.active[blockIdx.x] : (int)blockIdx.x;
+  const int b = a.active ? a.active[blockIdx.x] : (int)blockIdx.x + a.first;
   fddp_direction_body(a, b, sm, kp);
 }
 __global__ void __launch_bounds__(512) k_csqp_direction_generic(KArgs a, CsqpKPar kp) {
   extern __shared__ double sm[];
   if ((int)blockIdx.x >= a.n_active) return;
-  const int b = a.active ? a.active[blockIdx.x] : (int)blockIdx.x;
+  const int b = a.active ? a.active[blockIdx.x] : (int)blockIdx.x + a.first;
   csqp_direction_body(a, b, sm, kp);
 }
 __global__ void k_csqp_reset_rho(KArgs a, double base, double rho_min) {
   if ((int)blockIdx.x >= a.n_active) return;
-  const int b = a.active ? a.active[blockIdx.x] : (int)blockIdx.x;
+  const int b = a.active ? a.active[blockIdx.x] : (int)blockIdx.x + a.first;
   csqp_reset_rho_body(a, b, base, rho_min);
 }
 __global__ void k_csqp_calc_norms(KArgs a) {
   __shared__ double red[64];
   if ((int)blockIdx.x >= a.n_active) return;
-  const int b = a.active ? a.active[blockIdx.x] : (int)blockIdx.x;
+  const int b = a.active ? a.active[blockIdx.x] : (int)blockIdx.x + a.first;
   csqp_calc_norms_body(a, b, red);
 }
 __global__ void k_fill(double* p, size_t n, double v) {
@@ -809,6 +809,80 @@ int mimgpu_csqp_direction(mimgpu_ctx* c, const mimgpu_csqp_params* p, int with_k
   warn_generic(c, "CSQP");
   k_csqp_direction_generic<<<c->k.n_active, c->nt, c->smem_bytes, st>>>(c->k, kp);
   return post_launch(c, "k_csqp_direction_generic");
+}
+
+/* SolverCSQP::computeDirection for HOST-resident derivatives, end to end (row n3): the batch is cut into
+ * `n_chunks` slices; slice i is uploaded, its calc norms / rho reset (optional) and its whole ADMM loop
+ * run, and dx~ / du~ / lag_mul / y / z / KKT are downloaded on one of two internal streams, so the PCIe
+ * traffic of one slice overlaps the kernels of its neighbours.  Same results as mimgpu_upload +
+ * mimgpu_csqp_calc_norms + mimgpu_csqp_reset_rho + mimgpu_csqp_direction + mimgpu_download. */
+int mimgpu_csqp_direction_host(mimgpu_ctx* c, const mimgpu_derivs* d, const mimgpu_csqp_params* p, int with_kkt,
+                               int calc_norms, int reset_rho, double* dx_tilde, double* du_tilde, double* lag_mul,
+                               double* y, double* z, double* kkt, int32_t* qp_iters, int32_t n_chunks) {
+  if (!c || !d || !p) return fail(MIMGPU_ERR_INVALID, "null pointer");
+  if (p->rho_update_interval < 1 || p->max_qp_iters < 0) return fail(MIMGPU_ERR_INVALID, "bad CSQP parameters");
+  CU(cudaSetDevice(c->device));
+  const mimgpu_shape& sh = c->sh;
+  const size_t B = sh.B, T = sh.T, nx = sh.nx, nu = sh.nu, nc = T * sh.ng + sh.ngT;
+  if (c->k.active) return fail(MIMGPU_ERR_STATE, "mimgpu_csqp_direction_host with an active subset");
+  if (n_chunks < 1) n_chunks = 1;
+  if ((size_t)n_chunks > B) n_chunks = (int32_t)B;
+  for (int i = 0; i < 2; ++i)
+    if (!c->pipe_st[i]) CU(cudaStreamCreateWithFlags(&c->pipe_st[i], cudaStreamNonBlocking));
+  size_t n[20];
+  int rc = ensure_in_buf(c, n);
+  if (rc) return rc;
+  const double* src[20] = {d->Fx, d->Fu, d->Lxx, d->Lxu, d->Luu, d->Lx, d->Lu, d->fs, d->LxxT, d->LxT,
+                           d->Gx, d->Gu, d->g, d->g_lb, d->g_ub, d->GxT, d->gT, d->g_lbT, d->g_ubT, d->cost};
+  for (int i = 0; i < 19; ++i)
+    if (n[i] && !src[i]) return fail(MIMGPU_ERR_INVALID, "missing derivative array #" + std::to_string(i));
+  const double** slot[20];
+  deriv_slots(c->k, slot);
+  double* dst[20];
+  {
+    double* q = c->in_buf;
+    for (int i = 0; i < 20; ++i) {
+      dst[i] = q;
+      *slot[i] = (n[i] && src[i]) ? q : nullptr;
+      q += (n[i] + 1) & ~(size_t)1;
+    }
+  }
+  if (c->last_stream != c->pipe_st[0] && c->last_stream != c->pipe_st[1]) CU(cudaStreamSynchronize(c->last_stream));
+  c->attached = false; c->records_mode = false; c->fields_valid = true; c->k.pack = nullptr; c->pack_dirty = true;
+  inputs_changed(c);
+  const size_t per = (B + n_chunks - 1) / n_chunks;
+  for (size_t b0 = 0, ci = 0; b0 < B; b0 += per, ++ci) {
+    const size_t nb = (b0 + per <= B) ? per : B - b0;
+    cudaStream_t st = c->pipe_st[ci & 1];
+    for (int i = 0; i < 20; ++i) {
+      if (!(n[i] && src[i])) continue;
+      const size_t pb = n[i] / B;
+      CU(cudaMemcpyAsync(dst[i] + b0 * pb, src[i] + b0 * pb, nb * pb * sizeof(double), cudaMemcpyHostToDevice, st));
+    }
+    c->k.first = (int32_t)b0;
+    c->k.n_active = (int32_t)nb;
+    if (calc_norms) rc = mimgpu_csqp_calc_norms(c, st);
+    if (rc == MIMGPU_OK && reset_rho) rc = mimgpu_csqp_reset_rho(c, p, st);
+    if (rc == MIMGPU_OK) rc = mimgpu_csqp_direction(c, p, with_kkt, st);
+    c->k.first = 0;
+    c->k.n_active = (int32_t)B;
+    if (rc) return rc;
+    auto out = [&](double* h, int f, size_t pp) -> cudaError_t {
+      return (h && pp) ? cudaMemcpyAsync(h + b0 * pp, c->field[f] + b0 * pp, nb * pp * sizeof(double), cudaMemcpyDeviceToHost, st)
+                       : cudaSuccess;
+    };
+    CU(out(dx_tilde, MIMGPU_F_DX_TILDE, (T + 1) * nx));
+    CU(out(du_tilde, MIMGPU_F_DU_TILDE, T * nu));
+    CU(out(lag_mul, MIMGPU_F_LAG_MUL, (T + 1) * nx));
+    CU(out(y, MIMGPU_F_Y, nc));
+    CU(out(z, MIMGPU_F_Z, nc));
+    if (kkt) CU(cudaMemcpyAsync(kkt + b0, c->k.scal + (size_t)MIMGPU_S_KKT * B + b0, nb * sizeof(double), cudaMemcpyDeviceToHost, st));
+    if (qp_iters) CU(cudaMemcpyAsync(qp_iters + b0, c->k.qp_iters + b0, nb * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+  }
+  CU(cudaStreamSynchronize(c->pipe_st[0]));
+  CU(cudaStreamSynchronize(c->pipe_st[1]));
+  c->last_stream = c->pipe_st[0];
+  return MIMGPU_OK;
 }
 
 /* ------------------------------------------------------ solve() on the device */

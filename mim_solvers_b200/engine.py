@@ -213,6 +213,19 @@ class BatchEngine:
         check(self._lib.mimgpu_csqp_direction(self._ctx, C.byref(p), int(with_kkt), self.stream),
               "mimgpu_csqp_direction")
 
+    def csqp_direction_host(self, batch: OCPBatch, params=None, *, with_kkt=True, calc_norms=True, reset_rho=True,
+                            dx_tilde=None, du_tilde=None, lag_mul=None, y=None, z=None, kkt=None, qp_iters=None,
+                            n_chunks: int = 8):
+        """mimgpu_csqp_direction_host: host derivatives in, ADMM results out, overlapped slices; synchronous."""
+        p = params or _capi.default_csqp_params()
+        d = batch.derivs()
+        self._keep = batch
+        ptr = lambda a: None if a is None else a.ctypes.data
+        check(self._lib.mimgpu_csqp_direction_host(self._ctx, C.byref(d), C.byref(p), int(with_kkt), int(calc_norms),
+                                                   int(reset_rho), ptr(dx_tilde), ptr(du_tilde), ptr(lag_mul), ptr(y),
+                                                   ptr(z), ptr(kkt), ptr(qp_iters), int(n_chunks)),
+              "mimgpu_csqp_direction_host")
+
     # ---- data out ------------------------------------------------------------------
     def field(self, name: str) -> np.ndarray:
         out = np.empty(self._shape.field_shape(name))

@@ -314,3 +314,25 @@ def test_gpu_csqp_both_kernels(eng, oracle_lib, monkeypatch, switch, B, T, nx, n
     batch = make_random_batch(B, T, nx, nu, ng=ng, ngT=ngT, **kw)
     p = _capi.default_csqp_params(max_qp_iters=120)
     compare_engines_csqp(lambda b: eng(b), lambda b: oracle_lib.Oracle(b), batch, params=p, n_calls=2)
+
+
+@pytest.mark.parametrize("B,T,nx,nu,ng,ngT,n_chunks", [(37, 12, 12, 6, 3, 3, 5), (9, 10, 36, 12, 16, 0, 4), (5, 6, 7, 3, 4, 2, 2)])
+def test_gpu_csqp_direction_host_matches_stepwise(eng, B, T, nx, nu, ng, ngT, n_chunks):
+    """mimgpu_csqp_direction_host (overlapped slices, row n3) == upload + calc norms + rho reset + direction +
+    download, bit for bit; ragged last slice; a second call continues from the persistent y / rho state."""
+    from mim_solvers_b200 import _capi
+    from mim_solvers_b200.problems import make_random_batch
+    batch = make_random_batch(B, T, nx, nu, ng=ng, ngT=ngT)
+    p = _capi.default_csqp_params(max_qp_iters=60)
+    a = eng(batch)
+    b = eng(shape=batch.shape())
+    sh = batch.shape()
+    for call in range(2):
+        a.csqp_calc_norms(); a.csqp_reset_rho(p); a.csqp_direction(p, with_kkt=True)
+        out = {n: np.empty(sh.field_shape(n)) for n in ("dx_tilde", "du_tilde", "lag_mul", "y", "z")}
+        kkt, it = np.empty(sh.B), np.empty(sh.B, dtype=np.int32)
+        b.csqp_direction_host(batch, p, kkt=kkt, qp_iters=it, n_chunks=n_chunks, **out)
+        for n in out:
+            assert np.array_equal(out[n], a.field(n)), (call, n)
+        assert np.array_equal(kkt, a.scalar("KKT")) and np.array_equal(it, a.qp_iters)
+        assert np.array_equal(b.field("rho_vec"), a.field("rho_vec"))
