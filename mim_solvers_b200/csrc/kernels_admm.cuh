@@ -55,8 +55,8 @@ struct AdmmSmem {
 template <int NX, int NU>
 __host__ __device__ inline int admm_stage_doubles(int ng, bool staged, bool stage_g) {
   if (!staged) return 0;
-  const int gb = stage_g ? ng * (NX + NU) : 0, lb = NU * NU;   /* B buffer: [Gx Gu] (update) | LLT (gains) */
-  return 2 * NX * NU + (gb > lb ? gb : lb);
+  const int a = NX * NU + (stage_g ? ng * (NX + NU) : 0), b = NX * NU + NU * NU;
+  return a > b ? a : b;
 }
 template <int NX, int NU>
 __host__ __device__ inline AdmmSmem admm_layout(int ng, int ngT, int nwarps, int ric_total, int stage_doubles) {
@@ -124,7 +124,17 @@ __device__ __forceinline__ void wdot4_rtv(const double* M, int nrows, int nin, c
     const bool valid = o < nrows;
     const double* col = M + (size_t)(valid ? o : 0) * nin;
     double s0 = 0.0, s1 = 0.0, s2 = 0.0;
-    for (int r = q; r < nin; r += 4) {
+    /* four independent loads in flight per lane before the first FMA (global-memory operands: L2 latency) */
+    int r = q;
+    for (; r + 12 < nin; r += 16) {
+      const double m0 = col[r], m1 = col[r + 4], m2 = col[r + 8], m3 = col[r + 12];
+      if (U0) { s0 = fma(m0, v0[r], s0); s0 = fma(m1, v0[r + 4], s0); s0 = fma(m2, v0[r + 8], s0); s0 = fma(m3, v0[r + 12], s0); }
+      if (U12) {
+        s1 = fma(m0, v1[r], s1); s1 = fma(m1, v1[r + 4], s1); s1 = fma(m2, v1[r + 8], s1); s1 = fma(m3, v1[r + 12], s1);
+        s2 = fma(m0, v2[r], s2); s2 = fma(m1, v2[r + 4], s2); s2 = fma(m2, v2[r + 8], s2); s2 = fma(m3, v2[r + 12], s2);
+      }
+    }
+    for (; r < nin; r += 4) {
       const double mv = col[r];
       if (U0) s0 = fma(mv, v0[r], s0);
       if (U12) { s1 = fma(mv, v1[r], s1); s2 = fma(mv, v2[r], s2); }
@@ -405,134 +415,85 @@ static __device__ __noinline__ void admm_chain(const Prob& p, const AdmmScr& sc,
 }
 
 /* --------------------------------------------- gains and b_t after the backward chain */
-/* Per-warp software pipeline of the knot-parallel phases (STAGED shapes).  A warp walks its knots
- * t, t + nw, ...; while it works on knot t
- *   - the knot's FIRST block (K in the update phase, Fu in the gains phase: used first and last) sits
- *     in one of two shared-memory buffers, the next knot's copy streams into the other (TMA bulk copy
- *     issued by lane 0 at the top of the knot, completing on the buffer's mbarrier);
- *   - the SECOND block ([Gx Gu] / LLT) has one buffer, refilled for the next knot right after its
- *     last use in this knot;
- *   - the next knot's vectors are already on their way into registers.
- * So no step of a knot waits for global memory once the pipeline runs.  `WSeq` counts the loads
- * of this warp per buffer family (mbarrier phase parity); it persists across phases. */
-struct WSeq {
-  uint32_t a, b;
+/* Per-warp TMA stage of the knot-parallel phases (STAGED shapes): lane 0 pulls the knot's matrix
+ * blocks into the warp's shared-memory stage with bulk copies that complete on the warp's
+ * mbarrier; `seq` counts the loads of this warp (phase parity), it persists across phases. */
+struct WarpStage {
+  uint64_t* bar;
+  double* buf;
+  uint32_t seq;
+  __device__ __forceinline__ void begin(uint32_t bytes, int lane) { if (lane == 0) mbar_expect_tx(bar, bytes); }
+  __device__ __forceinline__ void copy(int off, const double* src, int ndoubles, int lane) {
+    if (lane == 0 && ndoubles > 0) tma_bulk_g2s(buf + off, src, (uint32_t)ndoubles * 8u, bar);
+  }
+  __device__ __forceinline__ void wait() { mbar_wait(bar, seq & 1u); ++seq; }
 };
-struct WarpPipe {
-  uint64_t* abar; /* [2] */
-  uint64_t* bbar; /* [1] */
-  double* abuf;   /* 2 x asz */
-  double* bbuf;
-  int asz;
-  uint32_t ia, wa, ib, wb; /* issue / wait counters */
-  __device__ __forceinline__ void issue_a(const double* src, int ndoubles, int lane) {
-    if (lane == 0) {
-      uint64_t* bar = abar + (ia & 1u);
-      mbar_expect_tx(bar, (uint32_t)ndoubles * 8u);
-      tma_bulk_g2s(abuf + (ia & 1u) * asz, src, (uint32_t)ndoubles * 8u, bar);
-    }
-    ++ia;
-  }
-  __device__ __forceinline__ const double* wait_a() {
-    mbar_wait(abar + (wa & 1u), (wa >> 1) & 1u);
-    const double* r = abuf + (wa & 1u) * asz;
-    ++wa;
-    return r;
-  }
-  /* two source blocks land back to back in the single B buffer */
-  __device__ __forceinline__ void issue_b(const double* s0, int n0, const double* s1, int n1, int lane) {
-    if (lane == 0) {
-      mbar_expect_tx(bbar, (uint32_t)(n0 + n1) * 8u);
-      tma_bulk_g2s(bbuf, s0, (uint32_t)n0 * 8u, bbar);
-      if (n1 > 0) tma_bulk_g2s(bbuf + n0, s1, (uint32_t)n1 * 8u, bbar);
-    }
-    ++ib;
-  }
-  __device__ __forceinline__ void wait_b() { mbar_wait(bbar, wb & 1u); ++wb; }
-};
-template <int NX, int NU>
-__device__ __forceinline__ WarpPipe warp_pipe(double* sm, const AdmmSmem& s, int warp, const WSeq& q) {
-  WarpPipe w;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sm + s.wbars) + 3 * warp;
-  double* ws = sm + s.ws0 + warp * s.wsn;
-  w.abar = bars; w.bbar = bars + 2;
-  w.abuf = ws + s.stg; w.asz = NX * NU; w.bbuf = w.abuf + 2 * NX * NU;
-  w.ia = w.wa = q.a; w.ib = w.wb = q.b;
-  return w;
-}
 
 /* Qu_t = qu_t + Fu_t^T tmp_t, k_t = Quu_t^-1 Qu_t (src/csqp.cpp:1083-1097), b_t = fs_{t+1} - Fu_t k_t;
  * one warp per knot.  qu_t was left in the Qu_ slot by admm_update. */
 template <int NX, int NU, bool STAGED>
 static __device__ __noinline__ void admm_gains(const Prob& p, const AdmmScr& sc, double* sm, const AdmmSmem& s,
-                                               WSeq& wseq) {
+                                               uint32_t& wseq) {
   extern __shared__ __align__(16) double sm_admm[];
   sm = sm_admm;
   using W = AdmmWs<NX, NU>;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
-  const int T = p.T;
   double* ws = sm + s.ws0 + warp * s.wsn;
   double *xs = ws + W::xs, *us = ws + W::us, *qu = ws + W::qu;
-  WarpPipe wp = warp_pipe<NX, NU>(sm, s, warp, wseq);
+  WarpStage stg{reinterpret_cast<uint64_t*>(sm + s.wbars) + warp, ws + s.stg, wseq};
   auto pull = [&](int t) { /* knot t's blocks and vectors -> L2 */
-    if (t >= T) return;
+    if (t >= p.T) return;
     pf_block(p.Fu + (size_t)t * NX * NU, NX * NU, lane);
     pf_block(p.L + (size_t)t * NU * NU, NU * NU, lane - 1);
     pf_vec(sc.tv + (size_t)t * NX, NX, lane - 2);
     pf_vec(p.fs + (size_t)(t + 1) * NX, NX, lane - 10);
     pf_vec(p.Qu + (size_t)t * NU, NU, lane - 18);
   };
-  double ntv0 = 0.0, ntv1 = 0.0, nfs0 = 0.0, nfs1 = 0.0, nqu = 0.0;
-  auto fetch = [&](int t) { /* knot t's vectors into registers */
-    if (t >= T) return;
-    if (lane < NX) { ntv0 = sc.tv[(size_t)t * NX + lane]; nfs0 = p.fs[(size_t)(t + 1) * NX + lane]; }
-    if (NX > 32 && lane + 32 < NX) { ntv1 = sc.tv[(size_t)t * NX + lane + 32]; nfs1 = p.fs[(size_t)(t + 1) * NX + lane + 32]; }
-    if (lane < NU) nqu = p.Qu[(size_t)t * NU + lane];
-  };
-  if (warp < T) {
-    if constexpr (STAGED) {
-      wp.issue_a(p.Fu + (size_t)warp * NX * NU, NX * NU, lane);
-      wp.issue_b(p.L + (size_t)warp * NU * NU, NU * NU, nullptr, 0, lane);
-    }
-    fetch(warp);
-  }
   pull(warp + nw);
-  for (int t = warp; t < T; t += nw) {
-    const int tn = t + nw;
-    const double fs0 = nfs0, fs1 = nfs1;
-    if (lane < NX) xs[lane] = ntv0;
-    if (NX > 32 && lane + 32 < NX) xs[lane + 32] = ntv1;
-    if (NX > 64) for (int i = lane + 64; i < NX; i += 32) xs[i] = sc.tv[(size_t)t * NX + i];
-    if (lane < NU) qu[lane] = nqu;
-    if constexpr (STAGED) { if (tn < T) wp.issue_a(p.Fu + (size_t)tn * NX * NU, NX * NU, lane); }
+  for (int t = warp; t < p.T; t += nw) {
+    const double* Fu = p.Fu + (size_t)t * NX * NU;
+    const double* L = p.L + (size_t)t * NU * NU;
+    if constexpr (STAGED) {
+      stg.begin((uint32_t)(NX * NU + NU * NU) * 8u, lane);
+      stg.copy(0, Fu, NX * NU, lane);
+      stg.copy(NX * NU, L, NU * NU, lane);
+    }
     pull(t + 2 * nw);
-    fetch(tn);
-    const double* mFu = p.Fu + (size_t)t * NX * NU;
-    const double* mL = p.L + (size_t)t * NU * NU;
-    if constexpr (STAGED) mFu = wp.wait_a();
+    /* the knot's vectors: all loads in flight at once */
+    double tv0 = 0.0, tv1 = 0.0, fs0 = 0.0, fs1 = 0.0, quv = 0.0;
+    if (lane < NX) { tv0 = sc.tv[(size_t)t * NX + lane]; fs0 = p.fs[(size_t)(t + 1) * NX + lane]; }
+    if (NX > 32 && lane + 32 < NX) { tv1 = sc.tv[(size_t)t * NX + lane + 32]; fs1 = p.fs[(size_t)(t + 1) * NX + lane + 32]; }
+    if (lane < NU) quv = p.Qu[(size_t)t * NU + lane];
+    if (lane < NX) xs[lane] = tv0;
+    if (NX > 32 && lane + 32 < NX) xs[lane + 32] = tv1;
+    if (NX > 64) for (int i = lane + 64; i < NX; i += 32) xs[i] = sc.tv[(size_t)t * NX + i];
+    if (lane < NU) qu[lane] = quv;
+    if constexpr (STAGED) stg.wait();
     __syncwarp();
-    wdot4<NX>(mFu, NU, xs, lane, [&](int a, double acc) {
-      double v = qu[a];
-      v += acc;
-      us[a] = v;                      /* Qu_t (us doubles as its buffer until the solve) */
-      p.Qu[(size_t)t * NU + a] = v;
-    });
-    __syncwarp();
-    double ki = (lane < NU) ? us[lane] : 0.0;
-    if constexpr (STAGED) { wp.wait_b(); mL = wp.bbuf; }
-    ki = wsolve_llt<NU>(mL, ki, lane);
-    __syncwarp();
-    if constexpr (STAGED) { if (tn < T) wp.issue_b(p.L + (size_t)tn * NU * NU, NU * NU, nullptr, 0, lane); }
-    if (lane < NU) { us[lane] = ki; p.kff[(size_t)t * NU + lane] = ki; }
-    __syncwarp();
-    waxpy<NX, NU>(mFu, us, lane, [&](int i, double acc) {
-      /* the lane that owns row i also loaded fs_{t+1}[i] */
-      const double f = (i < 32) ? fs0 : (i < 64) ? fs1 : p.fs[(size_t)(t + 1) * NX + i];
-      p.dxt[(size_t)(t + 1) * NX + i] = f - acc;
-    });
+    auto body = [&](const double* mFu, const double* mL) {
+      wdot4<NX>(mFu, NU, xs, lane, [&](int a, double acc) {
+        double v = qu[a];
+        v += acc;
+        us[a] = v;                      /* Qu_t (us doubles as its buffer until the solve) */
+        p.Qu[(size_t)t * NU + a] = v;
+      });
+      __syncwarp();
+      double ki = (lane < NU) ? us[lane] : 0.0;
+      ki = wsolve_llt<NU>(mL, ki, lane);
+      __syncwarp();
+      if (lane < NU) { us[lane] = ki; p.kff[(size_t)t * NU + lane] = ki; }
+      __syncwarp();
+      waxpy<NX, NU>(mFu, us, lane, [&](int i, double acc) {
+        /* the lane that owns row i also loaded fs_{t+1}[i] */
+        const double f = (i < 32) ? fs0 : (i < 64) ? fs1 : p.fs[(size_t)(t + 1) * NX + i];
+        p.dxt[(size_t)(t + 1) * NX + i] = f - acc;
+      });
+    };
+    if constexpr (STAGED) body(stg.buf, stg.buf + NX * NU);
+    else body(Fu, L);
     __syncwarp();
   }
-  wseq.a = wp.wa; wseq.b = wp.wb;
+  wseq = stg.seq;
   fence_proxy_async(); /* b_t -> the forward chain's TMA */
 }
 
@@ -544,7 +505,7 @@ static __device__ __noinline__ void admm_gains(const Prob& p, const AdmmScr& sc,
 template <int NX, int NU, bool STAGED>
 static __device__ __noinline__ void admm_update(const Prob& p, const AdmmScr& sc, double* sm, const AdmmSmem& s,
                                                 const mimgpu_csqp_params& q_, int iter, bool need_r, bool stage_g,
-                                                AdmmNorms& n, WSeq& wseq) {
+                                                AdmmNorms& n, uint32_t& wseq) {
   extern __shared__ __align__(16) double sm_admm[];
   sm = sm_admm;
   using W = AdmmWs<NX, NU>;
@@ -554,13 +515,12 @@ static __device__ __noinline__ void admm_update(const Prob& p, const AdmmScr& sc
   double* ws = sm + s.ws0 + warp * s.wsn;
   double *xs = ws + W::xs, *us = ws + W::us, *sqx = ws + W::qx, *squ = ws + W::qu, *sd = ws + W::ds, *se1 = sd + ngm,
          *se2 = se1 + ngm;
-  WarpPipe wp = warp_pipe<NX, NU>(sm, s, warp, wseq);
+  WarpStage stg{reinterpret_cast<uint64_t*>(sm + s.wbars) + warp, ws + s.stg, wseq};
   const bool check = (iter % q_.rho_update_interval) == 0;
   const bool heur = q_.update_rho_with_heuristic != 0;
   const bool dualg = check && !heur;
   const double alpha = q_.alpha, sigma = q_.sigma;
   double np_ = -CUDART_INF, nd_ = -CUDART_INF, npr = -CUDART_INF, ndr = -CUDART_INF; /* src/csqp.cpp:1201-1204 */
-  const bool sg = STAGED && stage_g && ng > 0; /* [Gx Gu] of the running knots go through the B buffer */
 
   /* row r of one knot: c given, z / y projection and the row-local norms (src/csqp.cpp:1231-1239) */
   auto project = [&](size_t o, int r, double c, double zp, double rho, double yo, double lo, double hi) {
@@ -601,65 +561,63 @@ static __device__ __noinline__ void admm_update(const Prob& p, const AdmmScr& sc
     pf_vec(p.kff + (size_t)t * NU, NU, lane - 19);
     if (need_r) { pf_vec(p.Lx + (size_t)t * NX, NX, lane - 11); pf_vec(p.Lu + (size_t)t * NU, NU, lane - 19); }
   };
-  /* vectors of the NEXT knot, in registers */
-  double nx0 = 0.0, nx1 = 0.0, nkf = 0.0, nlx0 = 0.0, nlx1 = 0.0, nlu = 0.0;
-  double nzp = 0.0, nrho = 1.0, nyo = 0.0, nlo = 0.0, nhi = 0.0;
-  auto fetch = [&](int t) {
-    if (t > T) return;
-    const bool last = (t == T);
-    const int nc = last ? ngT : ng;
-    const size_t o = (size_t)t * ng;
-    if (lane < NX) nx0 = p.dxt[(size_t)t * NX + lane];
-    if (NX > 32 && lane + 32 < NX) nx1 = p.dxt[(size_t)t * NX + lane + 32];
-    if (!last && lane < NU) nkf = p.kff[(size_t)t * NU + lane];
-    if (nc > 0 && nc <= 32 && lane < nc) { /* lane r holds row r's vectors */
-      const double* g = last ? p.gT : p.g + o;
-      const double* lb = last ? p.glbT : p.glb + o;
-      const double* ub = last ? p.gubT : p.gub + o;
-      nzp = p.z[o + lane]; nrho = p.rho[o + lane]; nyo = p.y[o + lane];
-      const double gv = g[lane];
-      nlo = lb[lane] - gv; nhi = ub[lane] - gv;
-    }
-    if (need_r && !last) {
-      if (lane < NX) nlx0 = p.Lx[(size_t)t * NX + lane];
-      if (NX > 32 && lane + 32 < NX) nlx1 = p.Lx[(size_t)t * NX + lane + 32];
-      if (lane < NU) nlu = p.Lu[(size_t)t * NU + lane];
-    }
-  };
-  auto issue_k = [&](int t) { if (STAGED && t < T) wp.issue_a(p.K + (size_t)t * NX * NU, NX * NU, lane); };
-  auto issue_g = [&](int t) {
-    if (sg && t < T) wp.issue_b(p.Gx + (size_t)t * ng * NX, ng * NX, p.Gu + (size_t)t * ng * NU, ng * NU, lane);
-  };
-  issue_k(warp);
-  issue_g(warp);
-  fetch(warp);
   pull(warp + nw);
   for (int t = warp; t <= T; t += nw) {
     const bool last = (t == T);
-    const int nc = last ? ngT : ng, tn = t + nw;
+    const int nc = last ? ngT : ng;
     const size_t o = (size_t)t * ng;
-    const bool rowreg = nc > 0 && nc <= 32;
-    /* ---- commit the prefetched vectors; start the next knot's loads */
-    const double zp = nzp, rho = nrho, yo = nyo, lo = nlo, hi = nhi;
-    if (lane < NX) { xs[lane] = nx0; p.dx[(size_t)t * NX + lane] = nx0; }
-    if (NX > 32 && lane + 32 < NX) { xs[lane + 32] = nx1; p.dx[(size_t)t * NX + lane + 32] = nx1; }
+    const double* Kg = p.K + (size_t)(last ? 0 : t) * NX * NU;
+    const double* Gxg = last ? p.GxT : (ng ? p.Gx + (size_t)t * ng * NX : nullptr);
+    const double* Gug = (last || !ng) ? nullptr : p.Gu + (size_t)t * ng * NU;
+    const bool sg = STAGED && stage_g && !last && ng > 0;
+    if constexpr (STAGED) {
+      if (!last) {
+        stg.begin((uint32_t)(NX * NU + (sg ? ng * (NX + NU) : 0)) * 8u, lane);
+        stg.copy(0, Kg, NX * NU, lane);
+        if (sg) { stg.copy(NX * NU, Gxg, ng * NX, lane); stg.copy(NX * NU + ng * NX, Gug, ng * NU, lane); }
+      }
+    }
+    pull(t + 2 * nw);
+    /* the knot's vectors: every load in flight before the first use */
+    double x0 = 0.0, x1 = 0.0, kf = 0.0, lx0 = 0.0, lx1 = 0.0, luv = 0.0;
+    double zp = 0.0, rho = 1.0, yo = 0.0, lo = 0.0, hi = 0.0;
+    const bool rowreg = nc > 0 && nc <= 32;   /* lane r holds row r's vectors */
+    if (lane < NX) x0 = p.dxt[(size_t)t * NX + lane];
+    if (NX > 32 && lane + 32 < NX) x1 = p.dxt[(size_t)t * NX + lane + 32];
+    if (!last && lane < NU) kf = p.kff[(size_t)t * NU + lane];
+    if (rowreg && lane < nc) {
+      const double* g = last ? p.gT : p.g + o;
+      const double* lb = last ? p.glbT : p.glb + o;
+      const double* ub = last ? p.gubT : p.gub + o;
+      zp = p.z[o + lane]; rho = p.rho[o + lane]; yo = p.y[o + lane];
+      const double gv = g[lane];
+      lo = lb[lane] - gv; hi = ub[lane] - gv;
+    }
+    if (need_r && !last) {
+      if (lane < NX) lx0 = p.Lx[(size_t)t * NX + lane];
+      if (NX > 32 && lane + 32 < NX) lx1 = p.Lx[(size_t)t * NX + lane + 32];
+      if (lane < NU) luv = p.Lu[(size_t)t * NU + lane];
+    }
+    if (lane < NX) { xs[lane] = x0; p.dx[(size_t)t * NX + lane] = x0; }
+    if (NX > 32 && lane + 32 < NX) { xs[lane + 32] = x1; p.dx[(size_t)t * NX + lane + 32] = x1; }
     if (NX > 64)
       for (int i = lane + 64; i < NX; i += 32) { const double x = p.dxt[(size_t)t * NX + i]; xs[i] = x; p.dx[(size_t)t * NX + i] = x; }
-    if (need_r && !last) { /* qx_t / qu_t start from Lx and Lu (the -sigma and G^T d terms follow) */
-      if (lane < NX) sqx[lane] = nlx0;
-      if (NX > 32 && lane + 32 < NX) sqx[lane + 32] = nlx1;
+    if (need_r && !last) { /* qx_t / qu_t start from Lx - sigma dx~ and Lu (the G^T d and -sigma du~ terms follow) */
+      if (lane < NX) sqx[lane] = lx0;
+      if (NX > 32 && lane + 32 < NX) sqx[lane + 32] = lx1;
       if (NX > 64) for (int i = lane + 64; i < NX; i += 32) sqx[i] = p.Lx[(size_t)t * NX + i];
-      if (lane < NU) squ[lane] = nlu;
+      if (lane < NU) squ[lane] = luv;
     }
-    if (!last && lane < NU) us[lane] = nkf;    /* k_t, replaced by du~_t below */
-    issue_k(tn);
-    pull(t + 2 * nw);
-    fetch(tn);
-    const double* K = p.K + (size_t)(last ? 0 : t) * NX * NU;
-    const double* Gx = last ? p.GxT : (ng ? p.Gx + (size_t)t * ng * NX : nullptr);
-    const double* Gu = (last || !ng) ? nullptr : p.Gu + (size_t)t * ng * NU;
-    if constexpr (STAGED) { if (!last) K = wp.wait_a(); }
+    if (!last && lane < NU) us[lane] = kf;    /* k_t, replaced by du~_t below */
+    if constexpr (STAGED) { if (!last) stg.wait(); }
     __syncwarp();
+    const double* K = Kg;
+    const double* Gx = Gxg;
+    const double* Gu = Gug;
+    if constexpr (STAGED) {
+      if (!last) K = stg.buf;
+      if (sg) { Gx = stg.buf + NX * NU; Gu = Gx + ng * NX; }
+    }
     if (!last) { /* du~ = -k - K dx~ (src/csqp.cpp:636-637); us[a] holds k_t[a] and is replaced by du~_t[a] */
       wdot4<NX>(K, NU, xs, lane, [&](int a, double acc) {
         double u = -us[a];
@@ -670,7 +628,6 @@ static __device__ __noinline__ void admm_update(const Prob& p, const AdmmScr& sc
       });
       __syncwarp();
     }
-    if (sg && !last) { wp.wait_b(); Gx = wp.bbuf; Gu = Gx + ng * NX; }
     if (nc) {
       /* c_r = sum_j Gx[r][j] dx~[j] + sum_a Gu[r][a] du~[a]: lanes over rows, columns split over lane groups */
       const int np2 = nc <= 4 ? 4 : nc <= 8 ? 8 : nc <= 16 ? 16 : 32, ph_n = 32 / np2;
@@ -681,20 +638,26 @@ static __device__ __noinline__ void admm_update(const Prob& p, const AdmmScr& sc
         const int rc = valid ? r : 0;
         double a1 = 0.0, a2 = 0.0, b1 = 0.0, b2 = 0.0;
         int j = ph;
-        for (; j + ph_n < NX; j += 2 * ph_n) {
-          const double g0 = Gx[rc + nc * j], g1 = Gx[rc + nc * (j + ph_n)];
+        for (; j + 3 * ph_n < NX; j += 4 * ph_n) { /* four independent loads in flight per lane */
+          const double g0 = Gx[rc + nc * j], g1 = Gx[rc + nc * (j + ph_n)], g2 = Gx[rc + nc * (j + 2 * ph_n)],
+                       g3 = Gx[rc + nc * (j + 3 * ph_n)];
           a1 = fma(g0, xs[j], a1);
           b1 = fma(g1, xs[j + ph_n], b1);
+          a1 = fma(g2, xs[j + 2 * ph_n], a1);
+          b1 = fma(g3, xs[j + 3 * ph_n], b1);
         }
-        if (j < NX) a1 = fma(Gx[rc + nc * j], xs[j], a1);
+        for (; j < NX; j += ph_n) a1 = fma(Gx[rc + nc * j], xs[j], a1);
         if (Gu) {
           int a = ph;
-          for (; a + ph_n < NU; a += 2 * ph_n) {
-            const double g0 = Gu[rc + nc * a], g1 = Gu[rc + nc * (a + ph_n)];
+          for (; a + 3 * ph_n < NU; a += 4 * ph_n) {
+            const double g0 = Gu[rc + nc * a], g1 = Gu[rc + nc * (a + ph_n)], g2 = Gu[rc + nc * (a + 2 * ph_n)],
+                         g3 = Gu[rc + nc * (a + 3 * ph_n)];
             a2 = fma(g0, us[a], a2);
             b2 = fma(g1, us[a + ph_n], b2);
+            a2 = fma(g2, us[a + 2 * ph_n], a2);
+            b2 = fma(g3, us[a + 3 * ph_n], b2);
           }
-          if (a < NU) a2 = fma(Gu[rc + nc * a], us[a], a2);
+          for (; a < NU; a += ph_n) a2 = fma(Gu[rc + nc * a], us[a], a2);
         }
         a1 += b1; a2 += b2;
         for (int off = np2; off < 32; off <<= 1) {
@@ -768,15 +731,14 @@ static __device__ __noinline__ void admm_update(const Prob& p, const AdmmScr& sc
           p.Qu[(size_t)t * NU + a] = v;
         }
       }
-    }
-    __syncwarp();
-    issue_g(tn);   /* the G buffer is free: every lane is past its last read */
-    if (need_r) { /* r_t = qx_t - K_t^T qu_t; K row-major NU x NX = col-major NX x NU */
-      waxpy<NX, NU>(K, squ, lane, [&](int i, double acc) { sc.rv[(size_t)t * NX + i] = sqx[i] - acc; });
+      __syncwarp();
+      if (need_r) { /* r_t = qx_t - K_t^T qu_t; K row-major NU x NX = col-major NX x NU */
+        waxpy<NX, NU>(K, squ, lane, [&](int i, double acc) { sc.rv[(size_t)t * NX + i] = sqx[i] - acc; });
+      }
     }
     __syncwarp();
   }
-  wseq.a = wp.wa; wseq.b = wp.wb;
+  wseq = stg.seq;
   fence_proxy_async(); /* r_t -> the backward chain's TMA */
   /* src/csqp.cpp:1201-1204: the four norms are -inf unless this is a check iteration */
   n.primal = n.dual = n.primal_rel = n.dual_rel = -CUDART_INF;
@@ -860,7 +822,7 @@ k_csqp_direction_admm(KArgs a, AdmmKPar kp) {
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
-  WSeq wseq{0u, 0u};  /* loads this warp has put through its pipeline buffers */
+  uint32_t wseq = 0u; /* loads this warp has put through its TMA stage */
   ChainSeq cseq{0, 0u};  /* ring position of the chains' TMA pipeline */
   AdmmScr sc;
   {
