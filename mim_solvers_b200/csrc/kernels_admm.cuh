@@ -795,9 +795,12 @@ static __device__ __noinline__ void admm_kkt(const Prob& p, double* sm, const Sm
 
 /* SolverCSQP::computeDirection (src/csqp.cpp:454-517): control flow of csqp_direction_body
  * (kernels_generic.cuh); USE_MMA selects the DMMA Riccati sweep for the full iterations. */
-template <int NX, int NU, bool USE_MMA>
+/* RIC: full Riccati sweeps by 0 = the shape-generic code, 1 = DMMA (double-buffered F / G), 2 = DMMA on the
+ * compact shared-memory layout (large shapes: Talos 76/32, 64/32, 48/24) */
+template <int NX, int NU, int RIC>
 __global__ void __launch_bounds__(AdmmTune<NX, NU>::MAXT, AdmmTune<NX, NU>::MINB)
 k_csqp_direction_admm(KArgs a, AdmmKPar kp) {
+  constexpr bool USE_MMA = RIC != 0;
   static_assert(NX % 2 == 0 && NU % 2 == 0 && NU <= 32, "16-byte rows, one lane per control in the gain solve");
   extern __shared__ __align__(16) double sm_admm[];
   if ((int)blockIdx.x >= a.n_active) return;
@@ -811,7 +814,8 @@ k_csqp_direction_admm(KArgs a, AdmmKPar kp) {
   double* gsm = sm + ss.uni; /* Riccati layouts live in the union region */
   const Smem gs = smem_layout(NX, NU, p.ng, p.ngT, a.stage_fx);
   RicSmem rs{};
-  if constexpr (USE_MMA) rs = ric_layout<NX, NU>(p.ng, p.ngT, true, AdmmTune<NX, NU>::RBUF);
+  if constexpr (RIC == 1) rs = ric_layout<NX, NU>(p.ng, p.ngT, true, AdmmTune<NX, NU>::RBUF);
+  if constexpr (RIC == 2) rs = ric_layout<NX, NU>(p.ng, p.ngT, true, 1, true);
   uint64_t* ric_bars = reinterpret_cast<uint64_t*>(sm + ss.bars);
   uint32_t ric_seq = 0u;
   if (threadIdx.x == 0) {
@@ -848,7 +852,7 @@ k_csqp_direction_admm(KArgs a, AdmmKPar kp) {
   n.primal = p.scal[MIMGPU_S_NORM_PRIMAL * B + b]; n.dual = p.scal[MIMGPU_S_NORM_DUAL * B + b];
   n.primal_rel = p.scal[MIMGPU_S_NORM_PRIMAL_REL * B + b]; n.dual_rel = p.scal[MIMGPU_S_NORM_DUAL_REL * B + b];
   if (q.equality_qp_initial_guess) { /* src/csqp.cpp:461-464 */
-    if constexpr (USE_MMA) st = ric_backward_mma<MODE_FULL, NX, NU>(p, gsm, rs, rp, ric_bars, ric_seq, true);
+    if constexpr (USE_MMA) st = ric_backward_mma<MODE_FULL, NX, NU, RIC == 2>(p, gsm, rs, rp, ric_bars, ric_seq, true);
     else st = admm_riccati_generic<MODE_EQ>(p, gsm, gs, rp, a.stage_fx);
     if (!st) { __syncthreads(); admm_forward_eq(p, gsm, gs); }
   }
@@ -863,7 +867,7 @@ k_csqp_direction_admm(KArgs a, AdmmKPar kp) {
   if (!st) {
     for (it = 1; it < q.max_qp_iters + 1; ++it) { /* src/csqp.cpp:470 */
       if (is_full(it)) {
-        if constexpr (USE_MMA) st = ric_backward_mma<MODE_FULL, NX, NU>(p, gsm, rs, rp, ric_bars, ric_seq);
+        if constexpr (USE_MMA) st = ric_backward_mma<MODE_FULL, NX, NU, RIC == 2>(p, gsm, rs, rp, ric_bars, ric_seq);
         else st = admm_riccati_generic<MODE_FULL>(p, gsm, gs, rp, a.stage_fx);
         if (st) break;
         __syncthreads();
@@ -916,24 +920,25 @@ k_csqp_direction_admm(KArgs a, AdmmKPar kp) {
 }
 
 /* ------------------------------------------------------------------- dispatch */
-/* shapes with a DMMA Riccati sweep for the full iterations | shapes whose full iterations run the
- * shape-generic sweep (constrained DMMA layout does not fit 227 KB, or NX % 4 != 0) */
-#define MIMGPU_ADMM_MMA_SHAPES(X) X(12, 6) X(36, 12) X(16, 8) X(8, 4) X(32, 16) X(4, 2)
-#define MIMGPU_ADMM_GEN_SHAPES(X) X(6, 2) X(10, 4) X(64, 32) X(76, 32) X(48, 24) X(24, 12)
 
-template <int NX, int NU, bool MMA>
+template <int NX, int NU, int MMA>   /* MMA: 0 none, 1 standard DMMA layout, 2 compact DMMA layout */
 static AdmmPlan admm_plan_t(const mimgpu_shape& sh, int stage_fx, int max_smem) {
   AdmmPlan pl{};
   const Smem gs = smem_layout(NX, NU, sh.ng, sh.ngT, stage_fx);
   pl.nt = AdmmTune<NX, NU>::MAXT;
   pl.nchain = ((4 * NX + 31) / 32) * 32;
   if (pl.nchain + 32 > pl.nt) return pl; /* compute warps + one producer warp */
-  for (int mma = MMA ? 1 : 0; mma >= 0; --mma) {
+  for (int pass = (MMA ? 0 : 1); pass < 2; ++pass) {
+    const int mma = pass == 0 ? MMA : 0;
     int ric_total = gs.total;
-    if (mma) {
-      if constexpr (MMA) {
-        const RicSmem rs = ric_layout<NX, NU>(sh.ng, sh.ngT, true, AdmmTune<NX, NU>::RBUF);
-        if (rs.total > ric_total) ric_total = rs.total;
+    if constexpr (MMA == 1) {
+      if (mma) { const RicSmem rs = ric_layout<NX, NU>(sh.ng, sh.ngT, true, AdmmTune<NX, NU>::RBUF); if (rs.total > ric_total) ric_total = rs.total; }
+    }
+    if constexpr (MMA == 2) {
+      if (mma) {
+        const RicSmem rs = ric_layout<NX, NU>(sh.ng, sh.ngT, true, 1, true);
+        if (rs.total > ric_total) ric_total = rs.total;   /* (csqp_kkt / forward_eq still use the generic layout's vectors) */
+        if ((NX + NU + 7) / 8 > 2 * (pl.nt / 32)) continue;    /* two tile rows per warp at most */
       }
     }
     /* stage Gx / Gu next to K only while MINB CTAs of this size still share an SM */
@@ -956,12 +961,9 @@ static AdmmPlan admm_plan_t(const mimgpu_shape& sh, int stage_fx, int max_smem) 
     pl.stage_g = stage_g;
     pl.chain_ns = ring_ns(ss);
     cudaError_t e;
-    if (mma) {
-      if constexpr (MMA) e = cudaFuncSetAttribute(k_csqp_direction_admm<NX, NU, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-      else e = cudaErrorInvalidValue;
-    } else {
-      e = cudaFuncSetAttribute(k_csqp_direction_admm<NX, NU, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-    }
+    if (mma == 1) e = cudaFuncSetAttribute(k_csqp_direction_admm<NX, NU, (MMA == 1 ? 1 : 0)>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    else if (mma == 2) e = cudaFuncSetAttribute(k_csqp_direction_admm<NX, NU, (MMA == 2 ? 2 : 0)>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    else e = cudaFuncSetAttribute(k_csqp_direction_admm<NX, NU, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
     if (e != cudaSuccess) { cudaGetLastError(); continue; }
     pl.ok = 1; pl.use_mma = mma; pl.ric_total = ric_total; pl.smem_bytes = bytes;
     return pl;
@@ -969,13 +971,22 @@ static AdmmPlan admm_plan_t(const mimgpu_shape& sh, int stage_fx, int max_smem) 
   return pl;
 }
 
+/* shapes with the standard DMMA Riccati sweep | large shapes on the compact DMMA layout | shape-generic sweeps */
+#define MIMGPU_ADMM_MMA_SHAPES(X) X(12, 6) X(36, 12) X(16, 8) X(8, 4) X(32, 16) X(4, 2)
+#define MIMGPU_ADMM_CMP_SHAPES(X) X(64, 32) X(76, 32) X(48, 24) X(24, 12)
+#define MIMGPU_ADMM_GEN_SHAPES(X) X(6, 2) X(10, 4)
+
 static inline AdmmPlan admm_plan(const mimgpu_shape& sh, int stage_fx, int max_smem) {
 #define X(NX_, NU_) \
-  if (sh.nx == NX_ && sh.nu == NU_) return admm_plan_t<NX_, NU_, true>(sh, stage_fx, max_smem);
+  if (sh.nx == NX_ && sh.nu == NU_) return admm_plan_t<NX_, NU_, 1>(sh, stage_fx, max_smem);
   MIMGPU_ADMM_MMA_SHAPES(X)
 #undef X
 #define X(NX_, NU_) \
-  if (sh.nx == NX_ && sh.nu == NU_) return admm_plan_t<NX_, NU_, false>(sh, stage_fx, max_smem);
+  if (sh.nx == NX_ && sh.nu == NU_) return admm_plan_t<NX_, NU_, 2>(sh, stage_fx, max_smem);
+  MIMGPU_ADMM_CMP_SHAPES(X)
+#undef X
+#define X(NX_, NU_) \
+  if (sh.nx == NX_ && sh.nu == NU_) return admm_plan_t<NX_, NU_, 0>(sh, stage_fx, max_smem);
   MIMGPU_ADMM_GEN_SHAPES(X)
 #undef X
   return AdmmPlan{};
@@ -987,18 +998,26 @@ static inline int admm_csqp_launch(const KArgs& a, const mimgpu_csqp_params& q, 
   kp.timing = timing;
   kp.q = q; kp.with_kkt = with_kkt; kp.ric_total = pl.ric_total; kp.nchain = pl.nchain; kp.stage_g = pl.stage_g; kp.chain_ns = pl.chain_ns;
   kp.acl = scratch[0]; kp.rv = scratch[1]; kp.tv = scratch[2];
-#define X(NX_, NU_)                                                                                         \
-  if (a.sh.nx == NX_ && a.sh.nu == NU_) {                                                                   \
-    if (pl.use_mma) k_csqp_direction_admm<NX_, NU_, true><<<a.n_active, pl.nt, pl.smem_bytes, st>>>(a, kp); \
-    else k_csqp_direction_admm<NX_, NU_, false><<<a.n_active, pl.nt, pl.smem_bytes, st>>>(a, kp);           \
-    return 0;                                                                                               \
+#define X(NX_, NU_)                                                                                      \
+  if (a.sh.nx == NX_ && a.sh.nu == NU_) {                                                                \
+    if (pl.use_mma) k_csqp_direction_admm<NX_, NU_, 1><<<a.n_active, pl.nt, pl.smem_bytes, st>>>(a, kp); \
+    else k_csqp_direction_admm<NX_, NU_, 0><<<a.n_active, pl.nt, pl.smem_bytes, st>>>(a, kp);            \
+    return 0;                                                                                            \
   }
   MIMGPU_ADMM_MMA_SHAPES(X)
 #undef X
-#define X(NX_, NU_)                                                                                         \
-  if (a.sh.nx == NX_ && a.sh.nu == NU_) {                                                                   \
-    k_csqp_direction_admm<NX_, NU_, false><<<a.n_active, pl.nt, pl.smem_bytes, st>>>(a, kp);                \
-    return 0;                                                                                               \
+#define X(NX_, NU_)                                                                                      \
+  if (a.sh.nx == NX_ && a.sh.nu == NU_) {                                                                \
+    if (pl.use_mma) k_csqp_direction_admm<NX_, NU_, 2><<<a.n_active, pl.nt, pl.smem_bytes, st>>>(a, kp); \
+    else k_csqp_direction_admm<NX_, NU_, 0><<<a.n_active, pl.nt, pl.smem_bytes, st>>>(a, kp);            \
+    return 0;                                                                                            \
+  }
+  MIMGPU_ADMM_CMP_SHAPES(X)
+#undef X
+#define X(NX_, NU_)                                                                                      \
+  if (a.sh.nx == NX_ && a.sh.nu == NU_) {                                                                \
+    k_csqp_direction_admm<NX_, NU_, 0><<<a.n_active, pl.nt, pl.smem_bytes, st>>>(a, kp);                 \
+    return 0;                                                                                            \
   }
   MIMGPU_ADMM_GEN_SHAPES(X)
 #undef X

@@ -46,8 +46,11 @@ struct RicCfg {
 struct RicSmem {
   int V, F0, F1, G0, G1, W, Qxu, Quu, L, K, Vx, tmp, Qv, kff, fs, d, rho, linv, col, vec, red, total;
 };
+/* compact = true (large shapes, FULL / EQ sweeps only): one F / G buffer, the Cholesky factor overwrites Quu in
+ * place, and Qxu lives in the G buffer (it is written after every warp is done reading G: ric_backward_mma
+ * <.., COMPACT = true> defers those stores) -- Talos (76, 32, ng = 32) then fits the 227 KB of one SM. */
 template <int NX, int NU>
-__host__ __device__ inline RicSmem ric_layout(int ng, int ngT, bool with_g, int nbuf = 2) {
+__host__ __device__ inline RicSmem ric_layout(int ng, int ngT, bool with_g, int nbuf = 2, bool compact = false) {
   RicSmem s;
   constexpr int N = NX + NU;
   const int ngm = ng > ngT ? ng : ngT;
@@ -58,7 +61,13 @@ __host__ __device__ inline RicSmem ric_layout(int ng, int ngT, bool with_g, int 
   s.G0 = RC_TAKE(with_g ? ng * N : 0); s.G1 = (nbuf == 2) ? RC_TAKE(with_g ? ng * N : 0) : s.G0;
   s.W = RC_TAKE(NX * N);
   s.K = s.W; /* K (nu x nx) is built after the last read of W and consumed before the next write */
-  s.Qxu = RC_TAKE(NX * NU); s.Quu = RC_TAKE(NU * NU); s.L = RC_TAKE(NU * NU);
+  if (compact) {
+    const int gsz = with_g ? ng * N : 0;
+    if (gsz >= NX * NU) s.Qxu = s.G0; else s.Qxu = RC_TAKE(NX * NU);
+    s.Quu = RC_TAKE(NU * NU); s.L = s.Quu;
+  } else {
+    s.Qxu = RC_TAKE(NX * NU); s.Quu = RC_TAKE(NU * NU); s.L = RC_TAKE(NU * NU);
+  }
   s.Vx = RC_TAKE(NX); s.tmp = RC_TAKE(NX); s.Qv = RC_TAKE(N); s.kff = RC_TAKE(NU); s.fs = RC_TAKE(NX);
   s.d = RC_TAKE(ngm); s.rho = RC_TAKE(ngm); s.linv = RC_TAKE(NU); s.col = RC_TAKE(2 * NU);
   s.vec = RC_TAKE(3 * NX + 2 * NU + 3 * ngm);
@@ -141,9 +150,10 @@ __device__ __forceinline__ void llt_solve_regs(const double* sL, const double* l
  * carve-up; `bars` are two initialised mbarriers (count 1) outside it; `seq` counts the TMA
  * loads this kernel has consumed on them so far (load n uses barrier and buffer n & 1 with
  * phase parity (n >> 1) & 1; the count carries over between sweeps of the same kernel). */
-template <int MODE, int NX, int NU>
+template <int MODE, int NX, int NU, bool COMPACT = false>
 static __device__ __noinline__ int ric_backward_mma(const Prob& p, double* sm, const RicSmem& s, const RicPar& rp,
                                              uint64_t* bars, uint32_t& seq, bool eq_run = false) {
+  static_assert(!COMPACT || MODE != MODE_DDP, "the compact layout overwrites Quu with its Cholesky factor");
   using C = RicCfg<NX, NU>;
   sm = as_shared(sm); /* keep LDS / STS addressing inside this out-of-line function */
   constexpr int N = C::N, XT = C::XT, NT = C::NT, KT = C::KT, UT = C::UT;
@@ -345,8 +355,10 @@ static __device__ __noinline__ int ric_backward_mma(const Prob& p, double* sm, c
         if (n >= NX) p.Qu[(size_t)t * NU + n - NX] = v;
       }
     }
-    /* ---- step C: Q = H + F^T W (+ G^T rho G), upper tile triangle */
-    for (int a = warp; a < NT; a += nw) {
+    /* ---- step C: Q = H + F^T W (+ G^T rho G), upper tile triangle.  COMPACT: the Qxu block shares its buffer
+     * with G, so its tiles wait in registers (qd) until every warp is done reading G. */
+    constexpr int QT0 = NX / 8, NQ = NT - QT0;   /* column tiles that can hold Qxu entries */
+    auto tile_row = [&](int a, double (*qd)[2]) {
       double fa[KT];
 #pragma unroll
       for (int kt = 0; kt < KT; ++kt) fa[kt] = F[(8 * a + g) * NX + 4 * kt + tq];
@@ -403,8 +415,12 @@ static __device__ __noinline__ int ric_backward_mma(const Prob& p, double* sm, c
             if (c < NX) {
               *reinterpret_cast<double2*>(V + r * NX + c) = make_double2(v0, v1);
             } else if (c < N) {
-              sQxu[r + NX * (c - NX)] = v0;
-              sQxu[r + NX * (c + 1 - NX)] = v1;
+              if constexpr (COMPACT) {
+                if (nt >= QT0) { qd[nt - QT0][0] = v0; qd[nt - QT0][1] = v1; }
+              } else {
+                sQxu[r + NX * (c - NX)] = v0;
+                sQxu[r + NX * (c + 1 - NX)] = v1;
+              }
             }
           } else if (r < N && c >= NX && c < N) {
             const int ru = r - NX, cu = c - NX;
@@ -412,14 +428,39 @@ static __device__ __noinline__ int ric_backward_mma(const Prob& p, double* sm, c
             if (cu + 1 >= ru) { sQuu[ru + NU * (cu + 1)] = v1; sQuu[cu + 1 + NU * ru] = v1; }
           }
         }
+    };
+    if constexpr (COMPACT) {
+      double qd[2][NQ > 0 ? NQ : 1][2];   /* at most two tile rows per warp (host: NT <= 2 * warps) */
+#pragma unroll
+      for (int ai = 0; ai < 2; ++ai) {
+        const int a = warp + ai * nw;
+        if (a < NT) tile_row(a, qd[ai]);
+      }
+      __syncthreads(); /* every warp is done with G: Qxu may land in its buffer */
+#pragma unroll
+      for (int ai = 0; ai < 2; ++ai) {
+        const int a = warp + ai * nw, r = 8 * a + g;
+        if (a < NT && r < NX) {
+#pragma unroll
+          for (int nt = QT0; nt < NT; ++nt) {
+            const int c = 8 * nt + 2 * tq;
+            if (nt >= a && c >= NX && c < N) {
+              sQxu[r + NX * (c - NX)] = qd[ai][nt - QT0][0];
+              sQxu[r + NX * (c + 1 - NX)] = qd[ai][nt - QT0][1];
+            }
+          }
+        }
+      }
+    } else {
+      for (int a = warp; a < NT; a += nw) tile_row(a, nullptr);
     }
     __syncthreads(); /* S3: Q, [Qx; Qu] complete */
-    if (!dbl && t > 0) issue(t - 1); /* single buffer: F, G of knot t are consumed */
+    if (!COMPACT && !dbl && t > 0) issue(t - 1); /* single buffer: F, G of knot t are consumed */
     /* ---- step E: computeGains (src/ddp.cpp:401-429) */
     int fail = 0;
     if (warp == 0) fail = warp_llt<NU>(sQuu, sL, linv, sm + s.col, lane);
     if (__syncthreads_or(fail)) { /* S4 */
-      if (!dbl && t > 0) { mbar_wait(bars + ((nload + 1) & 1u), ((nload + 1) >> 1) & 1u); seq = nload + 2; __syncthreads(); }
+      if (!COMPACT && !dbl && t > 0) { mbar_wait(bars + ((nload + 1) & 1u), ((nload + 1) >> 1) & 1u); seq = nload + 2; __syncthreads(); }
       else drain(t);
       return MIMGPU_STATUS_LLT | (t << 8);
     }
@@ -512,6 +553,7 @@ static __device__ __noinline__ int ric_backward_mma(const Prob& p, double* sm, c
       }
     }
     __syncthreads(); /* S6: M complete */
+    if (COMPACT && t > 0) issue(t - 1); /* compact layout: Qxu (in the G buffer) has been consumed by steps K and F */
     /* ---- step S: Vxx = (M + M^T)/2 + preg  (src/ddp.cpp:328-333) */
     int bad = 0;
     for (int e = tid; e < NX * NX; e += nth) {
