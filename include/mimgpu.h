@@ -358,6 +358,28 @@ int mimgpu_sqp_solve(mimgpu_ctx* ctx, const mimgpu_sqp_solve_params* p, const do
  * maxiter) of the last mimgpu_sqp_solve; either may be NULL. */
 int mimgpu_solve_info(mimgpu_ctx* ctx, int32_t* iters, int32_t* outcome, void* cuda_stream);
 
+/* ---- no-allocation entry point ------------------------------------------------ */
+/* NO COUNTERPART IN THE REFERENCE: added for callers that cannot
+ * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * SolverSQP::computeDirection without a ctx: the same kernel as mimgpu_sqp_direction on knot records
+ * (k_sqp_direction_small_gj), on the CURRENT device, enqueued on `cuda_stream`.  It calls no cudaMalloc /
+ * cudaFree / allocating routine: the kernel's scratch (the spill records its backward sweep hands to its
+ * forward sweep) is a static __device__ array of MIMGPU_NOALLOC_SCRATCH_BYTES that every GPU loading the
+ * library holds until exit.  Shapes: those mimgpu_get_record_layout accepts (ng = ngT = 0); sizes:
+ * mimgpu_noalloc_scratch_needed(shape) <= MIMGPU_NOALLOC_SCRATCH_BYTES (B <= 177 for UR5 nx=12 nu=6 T=100),
+ * otherwise MIMGPU_ERR_INVALID with the numbers in mimgpu_last_error.  All pointers are DEVICE memory:
+ *   records [B][problem_doubles] (16-byte aligned), cost [B] or NULL              -- inputs
+ *   dx [B][T+1][nx], du [B][T][nu], lag_mul [B][T+1][nx], status [B],
+ *   scalars [MIMGPU_S_COUNT][B] (rows KKT, GAP_NORM, MERIT, XGRAD_NORM, UGRAD_NORM are written) -- outputs
+ * Every call shares the one scratch array (it keeps the last call's contents; nothing in it needs clearing):
+ * calls that overlap on the GPU -- two streams, two host threads -- race.  Asynchronous. */
+#define MIMGPU_NOALLOC_SCRATCH_BYTES (32 * 1024 * 1024)
+int mimgpu_sqp_direction_records_noalloc(const mimgpu_shape* shape, const double* records, const double* cost,
+                                         const mimgpu_sqp_params* p, double* dx, double* du, double* lag_mul,
+                                         double* scalars, int32_t* status, void* cuda_stream);
+/* Scratch bytes a call with this shape needs (-1: shape not served by the record kernel). */
+int64_t mimgpu_noalloc_scratch_needed(const mimgpu_shape* shape);
+
 /* ---- data out -------------------------------------------------------------- */
 /* Copies one solver member of all B problems to host memory `dst`
  * (async on `stream`; synchronise the stream before reading). */

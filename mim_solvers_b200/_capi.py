@@ -32,6 +32,7 @@ SCALARS = dict(
     constraint_norm=10, dg=11, dq=12, cost=13, steplength=14, preg=15,
 )
 N_SCALARS = 16
+NOALLOC_SCRATCH_BYTES = 32 * 1024 * 1024   # MIMGPU_NOALLOC_SCRATCH_BYTES
 
 
 class Shape(C.Structure):
@@ -143,6 +144,7 @@ SYMBOLS = (
     "mimgpu_upload_records", "mimgpu_model_attach", "mimgpu_sqp_solve", "mimgpu_solve_info", "mimgpu_fddp_direction", "mimgpu_csqp_calc_norms", "mimgpu_csqp_reset_rho",
     "mimgpu_csqp_direction", "mimgpu_csqp_direction_host", "mimgpu_download", "mimgpu_field_ptr", "mimgpu_scalar",
     "mimgpu_iters_status", "mimgpu_converged", "mimgpu_summary_reduce", "mimgpu_launch_count", "mimgpu_stream_sync", "mimgpu_measure_peaks",
+    "mimgpu_sqp_direction_records_noalloc", "mimgpu_noalloc_scratch_needed",
 )
 
 _lib = None
@@ -185,6 +187,10 @@ def _declare(lib):
     lib.mimgpu_measure_peaks.argtypes = [C.c_int, c_double_p, c_double_p, c_double_p]
     lib.mimgpu_launch_count.argtypes = [vp]
     lib.mimgpu_launch_count.restype = i64
+    lib.mimgpu_sqp_direction_records_noalloc.argtypes = [C.POINTER(Shape), vp, vp, C.POINTER(SqpParams), vp, vp, vp, vp,
+                                                         vp, vp]
+    lib.mimgpu_noalloc_scratch_needed.argtypes = [C.POINTER(Shape)]
+    lib.mimgpu_noalloc_scratch_needed.restype = i64
     for name in SYMBOLS:
         f = getattr(lib, name)
         if f.restype is C.c_int and name not in ("mimgpu_abi_version",):

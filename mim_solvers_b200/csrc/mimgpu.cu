@@ -27,6 +27,10 @@ static int fail(int code, const std::string& msg) {
   g_err = msg;
   return code;
 }
+namespace mimgpu {
+/* for the entry points that live in other translation units (noalloc.cu) */
+void set_last_error(const std::string& msg) { g_err = msg; }
+}  // namespace mimgpu
 #define CU(call)                                                                                   \
   do {                                                                                             \
     cudaError_t e_ = (call);                                                                       \
