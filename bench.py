@@ -251,6 +251,10 @@ def traffic_entry(workload: str, B: int):
             tr = json.loads(tf.read_text()).get(workload)
             if tr and tr.get("B") == B:
                 return tr
+            if tr and tr.get("B"):   # one CTA per problem, no sharing between problems: bytes scale with B
+                k = B / tr["B"]
+                return {**tr, "dram_bytes_per_launch": tr["dram_bytes_per_launch"] * k,
+                        "source": tr["source"] + f", scaled x{k:.3g} to B={B}"}
     return None
 
 

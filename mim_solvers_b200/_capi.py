@@ -204,7 +204,8 @@ def load_library(path: os.PathLike | None = None):
     global _lib
     if _lib is not None and path is None:
         return _lib
-    p = Path(path) if path else LIB_PATH
+    # MIMGPU_LIB: another build of the same library (tuning variants, scripts/build_variant.sh)
+    p = Path(path) if path else Path(os.environ.get("MIMGPU_LIB") or LIB_PATH)
     if not p.exists():
         raise MimGpuError(
             f"{p} not found: build the CUDA extension first "

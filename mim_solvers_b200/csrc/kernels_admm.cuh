@@ -777,12 +777,21 @@ __host__ __device__ constexpr bool admm_staged() { return NX <= 36; }
 #ifndef MIMGPU_ADMM_C3_RBUF
 #define MIMGPU_ADMM_C3_RBUF 2
 #endif
+#ifndef MIMGPU_ADMM_C3_MAXT
+#define MIMGPU_ADMM_C3_MAXT 192
+#endif
+#ifndef MIMGPU_ADMM_C5_MAXT   /* the compact-layout shapes: 64/32, 76/32 */
+#define MIMGPU_ADMM_C5_MAXT 384
+#endif
+#ifndef MIMGPU_ADMM_N32_MAXT
+#define MIMGPU_ADMM_N32_MAXT 192
+#endif
 template <int NX, int NU> struct AdmmTune { static constexpr int MAXT = NX <= 16 ? 128 : 256, MINB = NX <= 16 ? 6 : 2, RBUF = 2; };
-template <> struct AdmmTune<36, 12> { static constexpr int MAXT = 192, MINB = MIMGPU_ADMM_C3_MINB, RBUF = MIMGPU_ADMM_C3_RBUF; };
+template <> struct AdmmTune<36, 12> { static constexpr int MAXT = MIMGPU_ADMM_C3_MAXT, MINB = MIMGPU_ADMM_C3_MINB, RBUF = MIMGPU_ADMM_C3_RBUF; };
 template <> struct AdmmTune<12, 6> { static constexpr int MAXT = 96, MINB = 8, RBUF = 2; };
-template <> struct AdmmTune<32, 16> { static constexpr int MAXT = 192, MINB = 2, RBUF = 2; };
-template <> struct AdmmTune<64, 32> { static constexpr int MAXT = 384, MINB = 1, RBUF = 2; };
-template <> struct AdmmTune<76, 32> { static constexpr int MAXT = 384, MINB = 1, RBUF = 2; };
+template <> struct AdmmTune<32, 16> { static constexpr int MAXT = MIMGPU_ADMM_N32_MAXT, MINB = 2, RBUF = 2; };
+template <> struct AdmmTune<64, 32> { static constexpr int MAXT = MIMGPU_ADMM_C5_MAXT, MINB = 1, RBUF = 2; };
+template <> struct AdmmTune<76, 32> { static constexpr int MAXT = MIMGPU_ADMM_C5_MAXT, MINB = 1, RBUF = 2; };
 template <> struct AdmmTune<48, 24> { static constexpr int MAXT = 256, MINB = 1, RBUF = 2; };
 
 template <int MODE>

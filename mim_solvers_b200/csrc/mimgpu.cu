@@ -782,10 +782,10 @@ int mimgpu_csqp_direction(mimgpu_ctx* c, const mimgpu_csqp_params* p, int with_k
   c->spill_packed = false;
   /* 16-byte rows / TMA bulk copies need 16-byte aligned sources (block sizes are even by construction) */
   const uintptr_t al = (uintptr_t)c->k.Fx | (uintptr_t)c->k.Fu | (uintptr_t)c->k.Gx | (uintptr_t)c->k.Gu;
-  /* Measured on B200 (profiles/sweep_r02_*.jsonl): the condensed-chain kernel wins from nx = 36 up (Solo12,
-   * 48/24, 64/32, Talos); below that a knot is too little work for a warp-per-knot phase and the
-   * sweep-by-sweep streaming kernel stays ahead (UR5: 108 k vs 87 k QP/s, 32/16: 11.3 k vs 10.8 k). */
-  const bool want_admm = c->csqp_admm || (c->sh.nx >= 36 && !c->csqp_stream) || !c->splan.ok;
+  /* Measured on B200 (profiles/variants_r02_v1.log): the condensed-chain kernel wins from nx = 32 up (32/16:
+   * 13.5 k vs 11.3 k QP/s; Solo12, 48/24, 64/32, Talos); below that a knot is too little work for a
+   * warp-per-knot phase and the sweep-by-sweep streaming kernel stays ahead (UR5: 108 k vs 80 k QP/s). */
+  const bool want_admm = c->csqp_admm || (c->sh.nx >= 32 && !c->csqp_stream) || !c->splan.ok;
   if (c->aplan.ok && !c->force_generic && want_admm && (al & 15) == 0) {
     if (!c->admm_scr[0]) {
       const size_t BT = (size_t)c->sh.B * c->sh.T, nx = c->sh.nx;

@@ -16,7 +16,7 @@ if [ "${NCU:-1}" = 1 ]; then
   # launch list of the default bench command (short: 20 steps), then one full capture per dominant kernel
   ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file $O/launches_$TAG.csv \
       python bench.py --steps 20 --warmup 3 --no-cpu > $O/ncu_list_$TAG.log 2>&1
-  W=C2_ur5_sqp K=k_sqp_direction_small_gj O=ncu_${TAG}_small_gj_sqp bash scripts/gpu_prof.sh
-  W=C3_solo12_csqp K=k_csqp_direction_admm O=ncu_${TAG}_csqp_admm_solo12 B=296 bash scripts/gpu_prof.sh
-  W=C5_talos_csqp K=k_csqp_direction_admm O=ncu_${TAG}_csqp_admm_talos B=148 bash scripts/gpu_prof.sh
+  W=C2_ur5_sqp K=k_sqp_direction_small_gj KS=k_sqp_direction_small_gjILi12ELi6E O=ncu_${TAG}_small_gj_sqp bash scripts/gpu_prof.sh
+  W=C3_solo12_csqp K=k_csqp_direction_admm KS=k_csqp_direction_admmILi36ELi12ELi1E O=ncu_${TAG}_csqp_admm_solo12 B=296 bash scripts/gpu_prof.sh
+  W=C5_talos_csqp K=k_csqp_direction_admm KS=k_csqp_direction_admmILi76ELi32ELi2E O=ncu_${TAG}_csqp_admm_talos B=148 bash scripts/gpu_prof.sh
 fi
