@@ -38,7 +38,8 @@ def solve_dense(batch, b):
 def check_against_dense(make_engine, tol=1e-8):
     from mim_solvers_b200 import _capi
     from mim_solvers_b200.problems import make_random_batch
-    for (B, T, nx, nu) in [(3, 6, 4, 2), (2, 9, 12, 6), (2, 4, 7, 3)]:
+    for (B, T, nx, nu) in [(3, 6, 4, 2), (2, 9, 12, 6), (2, 4, 7, 3), (2, 10, 36, 12), (1, 6, 16, 8), (2, 5, 32, 16),
+                           (1, 4, 24, 12), (1, 3, 64, 32), (1, 12, 8, 4)]:
         batch = make_random_batch(B, T, nx, nu)
         e = make_engine(batch)
         e.sqp_direction(_capi.default_sqp_params(preg=0.0, dreg=0.0))
