@@ -31,7 +31,7 @@ namespace mimgpu {
 /* Knot-packed HBM layout of the fast variant (built once per upload by k_pack_knots):
  *   input record of knot t  (REC doubles):  [fs_t | Lxx Lxu | Luu | Lx Lu | Fx Fu]
  *   terminal record         (TREC doubles): [fs_T | Lxx_T | Lx_T]
- *   spill record of knot t  (SREC doubles): [Vxx_t | Vx_t | K_t | k_t]
+ *   spill record of knot t  (SREC doubles): [triu(Vxx_t) | Vx_t | K_t | k_t]   (GjCfg::vrow)
  * so that the backward sweep stages a knot with ONE bulk copy (the whole record) and the
  * forward sweep with TWO: [Lx Lu Fx Fu](t) ++ [fs](t+1) is contiguous across two input
  * records, and [K k](t) ++ [Vxx Vx](t+1) is contiguous across two spill records. */
@@ -43,11 +43,35 @@ struct GjCfg {
   /* input record = backward stage */
   static constexpr int bFs = 0, bH = NX, bLuu = bH + NX * N, bL = bLuu + NU * NU, bF = bL + N, REC = bF + NX * N;
   static constexpr int TREC = NX + NX * NX + NX, tFs = 0, tLxx = NX, tLx = NX + NX * NX;
+  /* Vxx is symmetric: the spill keeps its upper triangle only, row i from the even column i & ~1 on
+   * (every row segment starts 16-byte aligned and has an even length; 84 instead of 144 doubles for NX = 12):
+   * element (i, n), n >= (i & ~1), sits at vrow(i) + n - (i & ~1) */
+  __host__ __device__ static constexpr int vrow(int i) {
+    const int e = i & ~1;
+    return e * NX - e * e / 2 + e + ((i & 1) ? NX - e : 0);
+  }
+  static constexpr int VTRI = vrow(NX);
   /* spill record */
-  static constexpr int sV = 0, sVx = NX * NX, sK = sVx + NX, sk = sK + NX * NU, SREC = sk + NU;
+  static constexpr int sV = 0, sVx = VTRI, sK = sVx + NX, sk = sK + NX * NU, SREC = sk + NU;
   /* forward stage: [Lx Lu | Fx Fu | fs+] ++ [K k | Vxx+ Vx+] */
   static constexpr int fL = 0, fF = N, fFs = fF + NX * N, FA = fFs + NX,
-                       fK = FA, fk = fK + NX * NU, fV = fk + NU, fVx = fV + NX * NX, STAGE_F = fVx + NX;
+                       fK = FA, fk = fK + NX * NU, fV = fk + NU, fVx = fV + VTRI, STAGE_F = fVx + NX;
+  /* (Vxx y)[i] from the packed triangle: columns n >= (i & ~1) come from row i, the others from
+   * row n (element (n, i)); two partial sums over even / odd n as in the dense row product */
+  __device__ static __forceinline__ double tri_row_dot(const double* V, const double* y, int i) {
+    const int e = i & ~1, rb = vrow(i) - e;
+    double a0 = 0.0, a1 = 0.0;
+#pragma unroll
+    for (int n = 0; n < NX; n += 2) {
+      const int cb = vrow(n) - n;                 /* n even: n & ~1 == n */
+      const int cb1 = vrow(n + 1) - n;
+      const double v0 = V[(n >= e) ? rb + n : cb + i];
+      const double v1 = V[(n >= e) ? rb + n + 1 : cb1 + i];
+      a0 = fma(v0, y[n], a0);
+      a1 = fma(v1, y[n + 1], a1);
+    }
+    return a0 + a1;
+  }
   static constexpr int STAGE_B = REC;
   static constexpr int STAGE = (STAGE_B > STAGE_F ? STAGE_B : STAGE_F);
   /* per-warp shared memory: two stages, the forward pass' vectors, two mbarriers */
@@ -141,10 +165,12 @@ __device__ __forceinline__ int small_backward_gj(const double* pk, double* sp, i
       const int i = 8 * it + g;
       if (i < NX) {
 #pragma unroll
+        const int e = i & ~1, rb = C::vrow(i) - e;
+#pragma unroll
         for (int nt = 0; nt < XT; ++nt) {
           const int n = 8 * nt + 2 * tq;
-          if (n < NX)
-            *reinterpret_cast<double2*>(sp + (size_t)t * C::SREC + C::sV + i * NX + n) =
+          if (n < NX && n >= e)                      /* upper triangle (from the even column i & ~1) only */
+            *reinterpret_cast<double2*>(sp + (size_t)t * C::SREC + C::sV + rb + n) =
                 make_double2(m[it][nt][0], m[it][nt][1]);
         }
         if (tq == 0) sp[(size_t)t * C::SREC + C::sVx + i] = vxg[it];
@@ -388,14 +414,7 @@ __device__ __forceinline__ void small_forward_gj(const Prob& p, const double* pk
   __syncwarp();
   double lam;
   {
-    double a0 = 0.0, a1 = 0.0;
-#pragma unroll
-    for (int j = 0; j < NX; j += 2) {
-      const double2 v2 = *reinterpret_cast<const double2*>(sp + C::sV + NX * lx + j);
-      a0 = fma(v2.x, sX[j], a0);
-      a1 = fma(v2.y, sX[j + 1], a1);
-    }
-    lam = (a0 + a1) + sp[C::sVx + lx];
+    lam = C::tri_row_dot(sp + C::sV, sX, lx) + sp[C::sVx + lx];
     if (gx) p.lag[lane] = lam;
   }
   __syncwarp();
@@ -444,19 +463,11 @@ __device__ __forceinline__ void small_forward_gj(const Prob& p, const double* pk
       p.dx[(size_t)(t + 1) * NX + lane] = x_n; sXn[lane] = x_n - fs_n;
     }
     __syncwarp();
-    /* lag_mul+ = Vxx+ (dx+ - fs+) + Vx+  (src/sqp.cpp:282-284, 296-298); Vxx+ is symmetric
-     * to rounding, so lane i reads its row as the contiguous column i */
+    /* lag_mul+ = Vxx+ (dx+ - fs+) + Vx+  (src/sqp.cpp:282-284, 296-298); Vxx+ arrives as its upper
+     * triangle (symmetric: the reference averages Vxx and its transpose, src/ddp.cpp:329) */
     double lam_n = 0.0;
     if (gx) {
-      double a0 = 0.0, a1 = 0.0;
-#pragma unroll
-      for (int jj = 0; jj < NX; jj += 2) {
-        const double2 v2 = *reinterpret_cast<const double2*>(st + C::fV + NX * lx + jj);
-        const double2 y2 = *reinterpret_cast<const double2*>(sXn + jj);
-        a0 = fma(v2.x, y2.x, a0);
-        a1 = fma(v2.y, y2.y, a1);
-      }
-      lam_n = (a0 + a1) + st[C::fVx + lx];
+      lam_n = C::tri_row_dot(st + C::fV, sXn, lx) + st[C::fVx + lx];
       p.lag[(size_t)(t + 1) * NX + lane] = lam_n; sLam[lane] = lam_n;
     }
     __syncwarp();
