@@ -336,6 +336,12 @@ class Engine {
     check(mimgpu_set_reg(ctx_, preg.data(), dreg.data(), stream_), "mimgpu_set_reg");
     sync();
   }
+  /* back to the scalar preg / dreg of the params struct (remove_reg_: a ctx that earlier received per-problem
+   * arrays must not keep using them) */
+  void clear_reg() {
+    check(mimgpu_set_reg(ctx_, nullptr, nullptr, stream_), "mimgpu_set_reg");
+    sync();
+  }
   void set_active(const std::vector<int32_t>* idx) {
     if (!idx) { check(mimgpu_set_active(ctx_, nullptr, -1, stream_), "mimgpu_set_active"); return; }
     check(mimgpu_set_active(ctx_, idx->data(), (int32_t)idx->size(), stream_), "mimgpu_set_active");
@@ -818,6 +824,7 @@ class BatchSolverCSQP : public BatchSolverBase {
   void computeDirection(bool recalcDiff = true) {
     if (recalcDiff && !engine_) calc(true);
     if (!remove_reg_) engine_->set_reg(preg_, dreg_);
+    else engine_->clear_reg();
     engine_->csqp_direction(params(), true);
     pullScalars(Mask(sh_.B, 1));
   }
@@ -1032,6 +1039,7 @@ class BatchSolverCSQP : public BatchSolverBase {
   Mask qp(const Mask& running) {
     if (remove_reg_) {
       setActive(running);
+      engine_->clear_reg();
       engine_->csqp_direction(params(), true);
       engine_->set_active(nullptr);
       return Mask(sh_.B, 0);

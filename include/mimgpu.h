@@ -366,7 +366,7 @@ int mimgpu_solve_info(mimgpu_ctx* ctx, int32_t* iters, int32_t* outcome, void* c
  * cudaFree / allocating routine: the kernel's scratch (the spill records its backward sweep hands to its
  * forward sweep) is a static __device__ array of MIMGPU_NOALLOC_SCRATCH_BYTES that every GPU loading the
  * library holds until exit.  Shapes: those mimgpu_get_record_layout accepts (ng = ngT = 0); sizes:
- * mimgpu_noalloc_scratch_needed(shape) <= MIMGPU_NOALLOC_SCRATCH_BYTES (B <= 238 for UR5 nx=12 nu=6 T=100),
+ * mimgpu_noalloc_scratch_needed(shape) <= MIMGPU_NOALLOC_SCRATCH_BYTES (B <= 177 for UR5 nx=12 nu=6 T=100),
  * otherwise MIMGPU_ERR_INVALID with the numbers in mimgpu_last_error.  All pointers are DEVICE memory:
  *   records [B][problem_doubles] (16-byte aligned), cost [B] or NULL              -- inputs
  *   dx [B][T+1][nx], du [B][T][nu], lag_mul [B][T+1][nx], status [B],

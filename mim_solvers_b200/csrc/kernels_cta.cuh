@@ -273,6 +273,19 @@ struct CtaTune { /* 4 lanes per right-hand side of the gain solve; MINB = reside
   static constexpr int MAXT = ((4 * (NX + 1) + 31) / 32) * 32 > 512 ? 512 : ((4 * (NX + 1) + 31) / 32) * 32;
   static constexpr int MINB = NX <= 16 ? 6 : NX <= 24 ? 4 : NX <= 36 ? 3 : 1;
 };
+/* per-shape overrides (build-time switches for tuning runs, scripts/build_variant.sh) */
+#ifdef MIMGPU_CTA_N64_MAXT
+template <> struct CtaTune<64, 32> { static constexpr int MAXT = MIMGPU_CTA_N64_MAXT, MINB = 1; };
+#endif
+#ifdef MIMGPU_CTA_N76_MAXT
+template <> struct CtaTune<76, 32> { static constexpr int MAXT = MIMGPU_CTA_N76_MAXT, MINB = 1; };
+#endif
+#ifdef MIMGPU_CTA_N32_MAXT
+#ifndef MIMGPU_CTA_N32_MINB
+#define MIMGPU_CTA_N32_MINB 3
+#endif
+template <> struct CtaTune<32, 16> { static constexpr int MAXT = MIMGPU_CTA_N32_MAXT, MINB = MIMGPU_CTA_N32_MINB; };
+#endif
 
 template <int NX, int NU, bool FDDP>
 __global__ void __launch_bounds__(CtaTune<NX, NU>::MAXT, CtaTune<NX, NU>::MINB) k_sqp_direction_cta(KArgs a, SqpKPar kp, int nbuf, int ns) {

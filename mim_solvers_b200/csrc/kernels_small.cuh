@@ -618,13 +618,13 @@ __global__ void __launch_bounds__(128) k_unpack_spill(KArgs a) {
   auto copy = [&](double* d, const double* s, int n) {
     for (int e = threadIdx.x; e < n; e += blockDim.x) d[e] = s[e];
   };
-  /* Vxx_ from the packed upper triangle (GjCfg::vrow), both halves */
+  /* Vxx_ from the spill: dense rows, or both halves from the packed upper triangle (GjCfg::TRI, vrow) */
   {
     double* V = a.Vxx + (b * (T + 1) + t) * NX * NX;
     for (int e = threadIdx.x; e < NX * NX; e += blockDim.x) {
       const int r = e / NX, c = e % NX;
-      const int i = r < c ? r : c, n = r < c ? c : r;     /* (i, n), i <= n */
-      V[e] = src[C::sV + C::vrow(i) + n - (i & ~1)];
+      const int i = (C::TRI && r > c) ? c : r, n = (C::TRI && r > c) ? r : c;     /* TRI: (i, n), i <= n */
+      V[e] = src[C::sV + C::vrow(i) + n - C::vstart(i)];
     }
   }
   copy(a.Vx + (b * (T + 1) + t) * NX, src + C::sVx, NX);

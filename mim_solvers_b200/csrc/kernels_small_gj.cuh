@@ -31,7 +31,7 @@ namespace mimgpu {
 /* Knot-packed HBM layout of the fast variant (built once per upload by k_pack_knots):
  *   input record of knot t  (REC doubles):  [fs_t | Lxx Lxu | Luu | Lx Lu | Fx Fu]
  *   terminal record         (TREC doubles): [fs_T | Lxx_T | Lx_T]
- *   spill record of knot t  (SREC doubles): [triu(Vxx_t) | Vx_t | K_t | k_t]   (GjCfg::vrow)
+ *   spill record of knot t  (SREC doubles): [Vxx_t or triu(Vxx_t) | Vx_t | K_t | k_t]   (GjCfg::TRI, vrow)
  * so that the backward sweep stages a knot with ONE bulk copy (the whole record) and the
  * forward sweep with TWO: [Lx Lu Fx Fu](t) ++ [fs](t+1) is contiguous across two input
  * records, and [K k](t) ++ [Vxx Vx](t+1) is contiguous across two spill records. */
@@ -43,10 +43,19 @@ struct GjCfg {
   /* input record = backward stage */
   static constexpr int bFs = 0, bH = NX, bLuu = bH + NX * N, bL = bLuu + NU * NU, bF = bL + N, REC = bF + NX * N;
   static constexpr int TREC = NX + NX * NX + NX, tFs = 0, tLxx = NX, tLx = NX + NX * NX;
-  /* Vxx is symmetric: the spill keeps its upper triangle only, row i from the even column i & ~1 on
-   * (every row segment starts 16-byte aligned and has an even length; 84 instead of 144 doubles for NX = 12):
-   * element (i, n), n >= (i & ~1), sits at vrow(i) + n - (i & ~1) */
+  /* Vxx is symmetric: from NX = MIMGPU_GJ_TRI_MIN_NX up the spill keeps its upper triangle only, row i from the
+   * even column i & ~1 on (every row segment starts 16-byte aligned and has an even length; 152 instead of 256
+   * doubles for NX = 16): element (i, n), n >= vstart(i), sits at vrow(i) + n - vstart(i).  Measured on B200
+   * (profiles/variants_r02_v2.log): a gain where the kernel is closer to the DRAM limit (NX = 16: 0.830 -> 0.766 ms),
+   * neutral to slightly negative for the 12/6 and 8/4 shapes, which are issue / LSU-bound and pay for the
+   * scalar triangle reads of the forward sweep -- those keep the dense rows. */
+#ifndef MIMGPU_GJ_TRI_MIN_NX
+#define MIMGPU_GJ_TRI_MIN_NX 16
+#endif
+  static constexpr bool TRI = NX >= MIMGPU_GJ_TRI_MIN_NX;
+  __host__ __device__ static constexpr int vstart(int i) { return TRI ? (i & ~1) : 0; }
   __host__ __device__ static constexpr int vrow(int i) {
+    if (!TRI) return i * NX;
     const int e = i & ~1;
     return e * NX - e * e / 2 + e + ((i & 1) ? NX - e : 0);
   }
@@ -56,19 +65,29 @@ struct GjCfg {
   /* forward stage: [Lx Lu | Fx Fu | fs+] ++ [K k | Vxx+ Vx+] */
   static constexpr int fL = 0, fF = N, fFs = fF + NX * N, FA = fFs + NX,
                        fK = FA, fk = fK + NX * NU, fV = fk + NU, fVx = fV + VTRI, STAGE_F = fVx + NX;
-  /* (Vxx y)[i] from the packed triangle: columns n >= (i & ~1) come from row i, the others from
-   * row n (element (n, i)); two partial sums over even / odd n as in the dense row product */
+  /* (Vxx y)[i]: dense rows, or from the packed triangle -- columns n >= (i & ~1) come from row i, the others from
+   * row n (element (n, i)); two partial sums over even / odd n in both cases */
   __device__ static __forceinline__ double tri_row_dot(const double* V, const double* y, int i) {
-    const int e = i & ~1, rb = vrow(i) - e;
     double a0 = 0.0, a1 = 0.0;
+    if constexpr (!TRI) {
 #pragma unroll
-    for (int n = 0; n < NX; n += 2) {
-      const int cb = vrow(n) - n;                 /* n even: n & ~1 == n */
-      const int cb1 = vrow(n + 1) - n;
-      const double v0 = V[(n >= e) ? rb + n : cb + i];
-      const double v1 = V[(n >= e) ? rb + n + 1 : cb1 + i];
-      a0 = fma(v0, y[n], a0);
-      a1 = fma(v1, y[n + 1], a1);
+      for (int n = 0; n < NX; n += 2) {
+        const double2 v2 = *reinterpret_cast<const double2*>(V + NX * i + n);
+        const double2 y2 = *reinterpret_cast<const double2*>(y + n);
+        a0 = fma(v2.x, y2.x, a0);
+        a1 = fma(v2.y, y2.y, a1);
+      }
+    } else {
+      const int e = i & ~1, rb = vrow(i) - e;
+#pragma unroll
+      for (int n = 0; n < NX; n += 2) {
+        const int cb = vrow(n) - n;                 /* n even: n & ~1 == n */
+        const int cb1 = vrow(n + 1) - n;
+        const double v0 = V[(n >= e) ? rb + n : cb + i];
+        const double v1 = V[(n >= e) ? rb + n + 1 : cb1 + i];
+        a0 = fma(v0, y[n], a0);
+        a1 = fma(v1, y[n + 1], a1);
+      }
     }
     return a0 + a1;
   }
@@ -165,11 +184,11 @@ __device__ __forceinline__ int small_backward_gj(const double* pk, double* sp, i
       const int i = 8 * it + g;
       if (i < NX) {
 #pragma unroll
-        const int e = i & ~1, rb = C::vrow(i) - e;
+        const int e = C::vstart(i), rb = C::vrow(i) - e;
 #pragma unroll
         for (int nt = 0; nt < XT; ++nt) {
           const int n = 8 * nt + 2 * tq;
-          if (n < NX && n >= e)                      /* upper triangle (from the even column i & ~1) only */
+          if (n < NX && n >= e)                      /* TRI: upper triangle (from the even column i & ~1) only */
             *reinterpret_cast<double2*>(sp + (size_t)t * C::SREC + C::sV + rb + n) =
                 make_double2(m[it][nt][0], m[it][nt][1]);
         }

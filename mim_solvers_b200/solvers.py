@@ -733,6 +733,8 @@ class SolverCSQP(_SolverBase):
             self.calc(True)
         if not self.remove_reg:
             self._engine.set_reg(self.preg, self.dreg)
+        else:
+            self._engine.set_reg(None, None)
         self._engine.csqp_direction(self._params(), with_kkt=True)
         self._pull_scalars(np.ones(self.B, dtype=bool))
 
@@ -785,6 +787,7 @@ class SolverCSQP(_SolverBase):
     def _qp(self, running):
         if self.remove_reg:
             self._set_active(running)
+            self._engine.set_reg(None, None)   # a ctx that earlier got per-problem reg arrays must not keep them
             self._engine.csqp_direction(self._params(), with_kkt=True)
             self._engine.set_active(None)
             return np.zeros(self.B, dtype=bool)

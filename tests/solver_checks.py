@@ -94,6 +94,29 @@ def check_regularisation_retry(factory):
     assert s.preg[1] > 1e-9 * 10 and s.preg[0] == 1e-9 and s.preg[2] == 1e-9, s.preg
 
 
+def check_remove_reg_on_reuse(factory):
+    """src/csqp.cpp:216-219: with remove_reg_ the QP runs with preg = dreg = 0.  A solver (and its ctx) that
+    earlier received per-problem regularisation arrays must not keep using them: its converged QP solution
+    must be the one of a fresh remove_reg solver (1e-6; a stale reg of 1e-2 moves it by 1e-3 and more)."""
+    p = make_lq(seed=11, constrained=True)
+
+    def tight(s):
+        s.eps_abs, s.eps_rel, s.max_qp_iters = 1e-10, 0.0, 8000
+        return s
+    a = tight(SolverCSQP(p, factory))
+    a.reg_min = 1e-2                       # visible regularisation: the first solve uploads per-problem arrays
+    a.solve(maxiter=1)
+    xs_reg = a.xs.copy()
+    a.remove_reg = True
+    a.solve(maxiter=1)
+    b = tight(SolverCSQP(p, factory))
+    b.remove_reg = True
+    b.solve(maxiter=1)
+    assert (a.qp_iters < a.max_qp_iters).all() and (b.qp_iters < b.max_qp_iters).all()
+    assert np.abs(xs_reg - b.xs).max() > 1e-4, "the regularised solve must differ visibly: weak test"
+    assert np.abs(a.xs - b.xs).max() < 1e-6 and np.abs(a.us - b.us).max() < 1e-6, np.abs(a.xs - b.xs).max()
+
+
 def check_fddp_lq(factory):
     p = make_lq(seed=9)
     s = SolverFDDP(p, factory)

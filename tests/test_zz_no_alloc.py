@@ -97,7 +97,7 @@ def test_no_alloc_rejects_sizes_beyond_the_static_scratch():
     lib = _capi.load_library()
     torch.cuda.set_device(0)
     params = _capi.default_sqp_params()
-    ok = _capi.Shape(238, 100, 12, 6, 0, 0)
+    ok = _capi.Shape(177, 100, 12, 6, 0, 0)
     need = lib.mimgpu_noalloc_scratch_needed(C.byref(ok))
     assert 0 < need <= _capi.NOALLOC_SCRATCH_BYTES
     d = torch.zeros(16, dtype=torch.float64, device="cuda")   # never touched: the call must fail before launching
@@ -119,7 +119,7 @@ def test_no_alloc_scratch_accounting_on_cpu():
     """No GPU needed: the size check is host arithmetic (spill records of all problems + qp_iters)."""
     lib = _capi.load_library()
     sh = _capi.Shape(10, 20, 12, 6, 0, 0)
-    srec = 84 + 12 + 12 * 6 + 6               # [triu(Vxx) | Vx | K | k] of one knot (kernels_small_gj.cuh::GjCfg)
+    srec = 12 * 12 + 12 + 12 * 6 + 6          # [Vxx | Vx | K | k] of one knot (kernels_small_gj.cuh::GjCfg, dense rows at nx = 12)
     spill = -(-10 * 21 * srec * 8 // 256) * 256
     assert lib.mimgpu_noalloc_scratch_needed(C.byref(sh)) == spill + 256
     assert lib.mimgpu_noalloc_scratch_needed(C.byref(_capi.Shape(10, 20, 36, 12, 0, 0))) == -1
