@@ -439,7 +439,8 @@ def run_workload(args, name, rank, world, local_rank, *, steps, warmup, e2e_step
         "value": value, "unit": UNIT, "ms_per_step": ms_per_step, "steps": steps, "warmup": warmup,
         "config": base_config(name, B, args.default_tol),
         "config_detail": {"input_layout": layout, "distinct_problems_per_gpu": min(B, args.distinct),
-                          "input_bytes_per_step": batch.nbytes()},
+                          "input_bytes_per_step": (int(dev_in[0].numel() + dev_in[1].numel()) * 8
+                                                   if layout == "knot-records" else batch.nbytes())},
         "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
         "qp_iters_histogram": qp_iters_hist, "clocks": clk.summary(),
         "batch_summary": {"max_kkt": float(summ["max_kkt"]), "sum_qp_iters": int(summ["sum_qp_iters"]),

@@ -38,7 +38,7 @@
 extern "C" {
 #endif
 
-#define MIMGPU_ABI_VERSION 2
+#define MIMGPU_ABI_VERSION 3
 
 /* ---- return codes ------------------------------------------------------ */
 #define MIMGPU_OK 0
@@ -106,17 +106,22 @@ typedef struct {
 /* Knot-record input layout (the HBM layout the warp-per-problem SQP kernel reads; available for
  * the shapes mimgpu_get_record_layout accepts, ng = ngT = 0).  One problem = T running-knot records
  * followed by one terminal record, problems back to back:
- *   running knot t : [fs_t | Lxx Lxu | Luu | Lx Lu | Fx Fu]   every block dense column-major
+ *   running knot t : [fs_t | Lxx | Lxu | Luu | Lx Lu | Fx Fu]
  *   terminal       : [fs_T | Lxx_T | Lx_T]
- * A packer writes each ActionData block with one memcpy at base + b * problem_doubles +
- * t * rec_doubles + off_*, exactly as it would into the field-major arrays. */
+ * Lxu, Fx, Fu and the vectors are the dense column-major Eigen image: one memcpy each at
+ * base + b * problem_doubles + t * rec_doubles + off_*.  The SYMMETRIC blocks Lxx, Luu, Lxx_T travel as
+ * their lower triangle when sym_packed != 0 (16 % fewer bytes over PCIe and from HBM): column j of an
+ * n x n block holds rows j .. n-1 -- contiguous in the Eigen image, one memcpy of n - j doubles from
+ * &M(j, j) -- at off + j * n - j (j - 1) / 2; the strict upper triangle is not transmitted (the hot path
+ * reads Lxx, Luu as symmetric; the reference's own are, up to rounding). */
 typedef struct {
   int32_t rec_doubles;     /* doubles of one running-knot record                    */
   int32_t term_doubles;    /* doubles of the terminal record                        */
   int32_t problem_doubles; /* T * rec_doubles + term_doubles                        */
   int32_t off_fs, off_Lxx, off_Lxu, off_Luu, off_Lx, off_Lu, off_Fx, off_Fu; /* in a running record */
   int32_t toff_fs, toff_Lxx, toff_Lx;                                          /* in the terminal record */
-  int32_t reserved[2];
+  int32_t sym_packed;      /* != 0: Lxx, Luu, Lxx_T are packed lower triangles (see above) */
+  int32_t reserved;
 } mimgpu_record_layout;
 
 /* SolverSQP / SolverFDDP direction parameters (src/sqp.cpp:91-97,224-242). */

@@ -78,7 +78,7 @@ class RecordLayout(C.Structure):
     """mimgpu_record_layout: block offsets (doubles) of the knot-record input layout."""
     _fields_ = [(n, C.c_int32) for n in (
         "rec_doubles", "term_doubles", "problem_doubles", "off_fs", "off_Lxx", "off_Lxu", "off_Luu",
-        "off_Lx", "off_Lu", "off_Fx", "off_Fu", "toff_fs", "toff_Lxx", "toff_Lx")] + [("reserved", C.c_int32 * 2)]
+        "off_Lx", "off_Lu", "off_Fx", "off_Fu", "toff_fs", "toff_Lxx", "toff_Lx", "sym_packed", "reserved")]
 
 
 class PolyModel(C.Structure):

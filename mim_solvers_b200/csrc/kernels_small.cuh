@@ -559,16 +559,23 @@ __global__ void __launch_bounds__(128) k_pack_knots(KArgs a, double* pack, int b
   auto copy = [&](double* d, const double* s, int n) {
     for (int e = threadIdx.x; e < n; e += blockDim.x) d[e] = s[e];
   };
+  /* symmetric block -> its packed lower triangle (GjCfg::sym_off); the upper triangle of the input is not read */
+  auto copy_sym = [&](double* d, const double* s, int n) {
+    for (int e = threadIdx.x; e < n * n; e += blockDim.x) {
+      const int i = e % n, j = e / n;
+      if (i >= j) d[C::sym_off(n, i, j)] = s[e];
+    }
+  };
   copy(dst + C::bFs, a.fs + (b * (T + 1) + t) * NX, NX);
   if (t == T) {
-    copy(dst + C::tLxx, a.LxxT + b * NX * NX, NX * NX);
+    copy_sym(dst + C::tLxx, a.LxxT + b * NX * NX, NX);
     copy(dst + C::tLx, a.LxT + b * NX, NX);
     return;
   }
   const size_t k = b * T + t;
-  copy(dst + C::bH, a.Lxx + k * NX * NX, NX * NX);
-  copy(dst + C::bH + NX * NX, a.Lxu + k * NX * NU, NX * NU);
-  copy(dst + C::bLuu, a.Luu + k * NU * NU, NU * NU);
+  copy_sym(dst + C::bH, a.Lxx + k * NX * NX, NX);
+  copy(dst + C::bLxu, a.Lxu + k * NX * NU, NX * NU);
+  copy_sym(dst + C::bLuu, a.Luu + k * NU * NU, NU);
   copy(dst + C::bL, a.Lx + k * NX, NX);
   copy(dst + C::bL + NX, a.Lu + k * NU, NU);
   copy(dst + C::bF, a.Fx + k * NX * NX, NX * NX);
@@ -591,16 +598,19 @@ __global__ void __launch_bounds__(128) k_unpack_records(const double* pack, Unpa
   auto copy = [&](double* d, const double* s, int n) {
     for (int e = threadIdx.x; e < n; e += blockDim.x) d[e] = s[e];
   };
+  auto copy_sym = [&](double* d, const double* s, int n) {   /* packed lower triangle -> full symmetric block */
+    for (int e = threadIdx.x; e < n * n; e += blockDim.x) d[e] = s[C::sym_off(n, e % n, e / n)];
+  };
   copy(o.fs + (b * (T + 1) + t) * NX, src + C::bFs, NX);
   if (t == T) {
-    copy(o.LxxT + b * NX * NX, src + C::tLxx, NX * NX);
+    copy_sym(o.LxxT + b * NX * NX, src + C::tLxx, NX);
     copy(o.LxT + b * NX, src + C::tLx, NX);
     return;
   }
   const size_t k = b * T + t;
-  copy(o.Lxx + k * NX * NX, src + C::bH, NX * NX);
-  copy(o.Lxu + k * NX * NU, src + C::bH + NX * NX, NX * NU);
-  copy(o.Luu + k * NU * NU, src + C::bLuu, NU * NU);
+  copy_sym(o.Lxx + k * NX * NX, src + C::bH, NX);
+  copy(o.Lxu + k * NX * NU, src + C::bLxu, NX * NU);
+  copy_sym(o.Luu + k * NU * NU, src + C::bLuu, NU);
   copy(o.Lx + k * NX, src + C::bL, NX);
   copy(o.Lu + k * NU, src + C::bL + NX, NU);
   copy(o.Fx + k * NX * NX, src + C::bF, NX * NX);
@@ -770,8 +780,8 @@ static inline int small_record_offsets(const mimgpu_shape& s, int out[16]) {
   if (s.nx == NX_ && s.nu == NU_) {                                                                   \
     if constexpr (NX_ % 4 == 0) {                                                                     \
       using C = GjCfg<NX_, NU_>;                                                                      \
-      const int v[16] = {C::REC, C::TREC, (int)C::pack_doubles(s.T), C::bFs, C::bH, C::bH + NX_ * NX_, C::bLuu, C::bL, \
-                         C::bL + NX_, C::bF, C::bF + NX_ * NX_, C::tFs, C::tLxx, C::tLx, 0, 0};      \
+      const int v[16] = {C::REC, C::TREC, (int)C::pack_doubles(s.T), C::bFs, C::bH, C::bLxu, C::bLuu, C::bL,          \
+                         C::bL + NX_, C::bF, C::bF + NX_ * NX_, C::tFs, C::tLxx, C::tLx, C::SYM ? 1 : 0, 0};       \
       for (int i = 0; i < 16; ++i) out[i] = v[i];                                                     \
       return 0;                                                                                       \
     }                                                                                                 \

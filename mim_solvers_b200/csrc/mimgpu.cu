@@ -458,7 +458,8 @@ int mimgpu_get_record_layout(const mimgpu_ctx* c, mimgpu_record_layout* out) {
   out->off_fs = v[3]; out->off_Lxx = v[4]; out->off_Lxu = v[5]; out->off_Luu = v[6]; out->off_Lx = v[7];
   out->off_Lu = v[8]; out->off_Fx = v[9]; out->off_Fu = v[10];
   out->toff_fs = v[11]; out->toff_Lxx = v[12]; out->toff_Lx = v[13];
-  out->reserved[0] = out->reserved[1] = 0;
+  out->sym_packed = v[14];
+  out->reserved = 0;
   return MIMGPU_OK;
 }
 

@@ -81,17 +81,27 @@ class BatchEngine:
         record layout (host side, numpy).  Returns a [B, problem_doubles] float64 array."""
         L = self.record_layout()
         B, T, nx, nu = batch.B, batch.T, batch.nx, batch.nu
-        rec = np.empty((B, L.problem_doubles)) if out is None else out
+        rec = np.zeros((B, L.problem_doubles)) if out is None else out
         run = rec[:, :T * L.rec_doubles].reshape(B, T, L.rec_doubles)
         term = rec[:, T * L.rec_doubles:]
         A = batch.arrays
-        for name, off, n in (("Lxx", L.off_Lxx, nx * nx), ("Lxu", L.off_Lxu, nx * nu), ("Luu", L.off_Luu, nu * nu),
-                             ("Lx", L.off_Lx, nx), ("Lu", L.off_Lu, nu), ("Fx", L.off_Fx, nx * nx),
-                             ("Fu", L.off_Fu, nx * nu)):
+
+        def put_sym(dst, off, M, n):
+            """symmetric n x n block (storage [..., col, row]): packed lower triangle, column j = rows j..n-1"""
+            if not L.sym_packed:
+                dst[..., off:off + n * n] = M.reshape(M.shape[:-2] + (n * n,))
+                return
+            for j in range(n):
+                o = off + j * n - j * (j - 1) // 2
+                dst[..., o:o + n - j] = M[..., j, j:]
+        put_sym(run, L.off_Lxx, A["Lxx"].reshape(B, T, nx, nx), nx)
+        put_sym(run, L.off_Luu, A["Luu"].reshape(B, T, nu, nu), nu)
+        for name, off, n in (("Lxu", L.off_Lxu, nx * nu), ("Lx", L.off_Lx, nx), ("Lu", L.off_Lu, nu),
+                             ("Fx", L.off_Fx, nx * nx), ("Fu", L.off_Fu, nx * nu)):
             run[:, :, off:off + n] = A[name].reshape(B, T, n)
         run[:, :, L.off_fs:L.off_fs + nx] = A["fs"][:, :T]
         term[:, L.toff_fs:L.toff_fs + nx] = A["fs"][:, T]
-        term[:, L.toff_Lxx:L.toff_Lxx + nx * nx] = A["LxxT"].reshape(B, nx * nx)
+        put_sym(term, L.toff_Lxx, A["LxxT"].reshape(B, nx, nx), nx)
         term[:, L.toff_Lx:L.toff_Lx + nx] = A["LxT"]
         return rec
 

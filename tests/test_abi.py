@@ -24,7 +24,7 @@ def test_header_symbols_exported(lib):
     assert declared == set(_capi.SYMBOLS), declared ^ set(_capi.SYMBOLS)
     for s in declared:
         assert hasattr(lib, s), s
-    assert lib.mimgpu_abi_version() == 2
+    assert lib.mimgpu_abi_version() == 3
 
 
 def test_struct_sizes_match_header():
