@@ -294,6 +294,7 @@ def run_workload(args, name, rank, world, local_rank, *, steps, warmup, e2e_step
     if dev_in is None:
         dev_in = {k: torch.from_numpy(v).to(dev) for k, v in batch.arrays.items()}
         eng.attach_device(dev_in)
+    input_bytes = (int(dev_in[0].numel() + dev_in[1].numel()) * 8 if layout == "knot-records" else batch.nbytes())
     if solver == "csqp":
         p = csqp_bench_params() if not args.default_tol else _capi.default_csqp_params()
         eng.csqp_calc_norms()
@@ -439,8 +440,7 @@ def run_workload(args, name, rank, world, local_rank, *, steps, warmup, e2e_step
         "value": value, "unit": UNIT, "ms_per_step": ms_per_step, "steps": steps, "warmup": warmup,
         "config": base_config(name, B, args.default_tol),
         "config_detail": {"input_layout": layout, "distinct_problems_per_gpu": min(B, args.distinct),
-                          "input_bytes_per_step": (int(dev_in[0].numel() + dev_in[1].numel()) * 8
-                                                   if layout == "knot-records" else batch.nbytes())},
+                          "input_bytes_per_step": input_bytes},
         "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
         "qp_iters_histogram": qp_iters_hist, "clocks": clk.summary(),
         "batch_summary": {"max_kkt": float(summ["max_kkt"]), "sum_qp_iters": int(summ["sum_qp_iters"]),

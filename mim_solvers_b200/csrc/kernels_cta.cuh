@@ -312,7 +312,13 @@ __global__ void __launch_bounds__(CtaTune<NX, NU>::MAXT, CtaTune<NX, NU>::MINB) 
     const double gap = gap_norm_all(p, um + gs.red);
     if (threadIdx.x == 0) p.scal[MIMGPU_S_GAP_NORM * (size_t)p.B + b] = gap;
   }
+#ifdef MIMGPU_RIC_TIMING
+  const long long tk0_ = clock64();
+#endif
   const int st = ric_backward_mma<MODE_DDP, NX, NU>(p, um, rs, rp, bars, seq);
+#ifdef MIMGPU_RIC_TIMING
+  const long long tk1_ = clock64();
+#endif
   if (threadIdx.x == 0) { a.status[b] = st; a.qp_iters[b] = 0; }
   if (st) {
     if (!FDDP) { /* gap norm / merit are computed before the backward pass in the reference */
@@ -338,6 +344,16 @@ __global__ void __launch_bounds__(CtaTune<NX, NU>::MAXT, CtaTune<NX, NU>::MINB) 
   } else {
     sqp_forward_kkt_ool(p, um, gs, kp.mu_dynamic, a.stage_fx);
   }
+#ifdef MIMGPU_RIC_TIMING
+  __syncthreads();
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    const long long tk2_ = clock64();
+    printf("ric timing nx=%d nu=%d T=%d (cycles, CTA 0): load+pack %lld  V+B %lld  D+C %lld  LLT %lld  solve %lld  F %lld  "
+           "sym %lld  close+spill %lld | backward %lld forward %lld\n", NX, NU, p.T, g_ric_t[0], g_ric_t[1], g_ric_t[2],
+           g_ric_t[3], g_ric_t[4], g_ric_t[5], g_ric_t[6], g_ric_t[7], tk1_ - tk0_, tk2_ - tk1_);
+    for (int i = 0; i < 16; ++i) g_ric_t[i] = 0;
+  }
+#endif
 }
 
 #define MIMGPU_CTA_SHAPES(X) X(36, 12) X(64, 32) X(76, 32) X(32, 16) X(16, 8) X(24, 12) X(48, 24)

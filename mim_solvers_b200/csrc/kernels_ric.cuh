@@ -145,6 +145,24 @@ __device__ __forceinline__ void llt_solve_regs(const double* sL, const double* l
   }
 }
 
+/* Per-step clock64 timer of CTA 0 (build-time debug switch MIMGPU_RIC_TIMING, scripts/build_variant.sh): cycles of
+ * thread 0 between the step barriers of ric_backward_mma, printed by the calling kernel. */
+#ifdef MIMGPU_RIC_TIMING
+static __device__ long long g_ric_t[16];
+#define RIC_T0() long long rt0_ = clock64()
+#define RIC_T(slot)                                                     \
+  do {                                                                  \
+    if (blockIdx.x == 0 && threadIdx.x == 0) {                          \
+      const long long c_ = clock64();                                   \
+      g_ric_t[slot] += c_ - rt0_;                                       \
+      rt0_ = c_;                                                        \
+    }                                                                   \
+  } while (0)
+#else
+#define RIC_T0() do {} while (0)
+#define RIC_T(slot) do {} while (0)
+#endif
+
 /* ------------------------------------------------------------ the backward sweep */
 /* Returns 0 or the status word (uniform over the CTA).  `sm` is the base of a RicSmem
  * carve-up; `bars` are two initialised mbarriers (count 1) outside it; `seq` counts the TMA
@@ -268,6 +286,7 @@ static __device__ __noinline__ int ric_backward_mma(const Prob& p, double* sm, c
   }
 
   const int grp = tid >> 2, q4 = tid & 3, ngrp = nth >> 2;
+  RIC_T0();
   for (int t = T - 1; t >= 0; --t) {
     const uint32_t nload = seq0 + (uint32_t)(T - 1 - t);
     __syncthreads(); /* S0: knot t+1 is complete (V, Vx final; every buffer of it consumed) */
@@ -280,6 +299,7 @@ static __device__ __noinline__ int ric_backward_mma(const Prob& p, double* sm, c
     }
     mbar_wait(bars + (nload & 1u), (nload >> 1) & 1u);
     __syncthreads(); /* S1: vector pack visible */
+    RIC_T(0);
     const double* F = sm + ((nload & 1u) ? s.F1 : s.F0);
     const double* G = sm + ((nload & 1u) ? s.G1 : s.G0);
     const bool gx_on = FULL && ng && t > 0; /* x0 is fixed: src/csqp.cpp:734,745,777 */
@@ -332,6 +352,7 @@ static __device__ __noinline__ int ric_backward_mma(const Prob& p, double* sm, c
       }
     }
     __syncthreads(); /* S2: W, tmp, d complete */
+    RIC_T(1);
     /* ---- step D: [Qx; Qu] (src/ddp.cpp:291-292,301-302; src/csqp.cpp:727-739,755-759) */
     for (int o0 = 0; o0 < N; o0 += ngrp) {
       const int n = o0 + grp;
@@ -455,6 +476,7 @@ static __device__ __noinline__ int ric_backward_mma(const Prob& p, double* sm, c
       for (int a = warp; a < NT; a += nw) tile_row(a, nullptr);
     }
     __syncthreads(); /* S3: Q, [Qx; Qu] complete */
+    RIC_T(2);
     if (!COMPACT && !dbl && t > 0) issue(t - 1); /* single buffer: F, G of knot t are consumed */
     /* ---- step E: computeGains (src/ddp.cpp:401-429) */
     int fail = 0;
@@ -464,6 +486,7 @@ static __device__ __noinline__ int ric_backward_mma(const Prob& p, double* sm, c
       else drain(t);
       return MIMGPU_STATUS_LLT | (t << 8);
     }
+    RIC_T(3);
     /* K = Quu^-1 Qxu^T (nx right-hand sides) and k = Quu^-1 Qu: QS lanes share one right-hand
      * side, lane q owns rows i = q (mod QS); per elimination step the owner of row j scales it
      * and broadcasts it by shuffle, every lane updates its own rows (independent FMAs).  Each
@@ -514,6 +537,7 @@ static __device__ __noinline__ int ric_backward_mma(const Prob& p, double* sm, c
     }
     for (int e = tid; e < NU * NU; e += nth) p.L[(size_t)t * NU * NU + e] = sL[e];
     __syncthreads(); /* S5: K, k complete */
+    RIC_T(4);
     for (int e = tid; e < NU * NX; e += nth) p.K[(size_t)t * NX * NU + e] = sK[e];
     /* ---- step F: M = Qxx - Qxu K on the upper tiles; Vx = Qx - K^T Qu; Quuk */
     {
@@ -553,6 +577,7 @@ static __device__ __noinline__ int ric_backward_mma(const Prob& p, double* sm, c
       }
     }
     __syncthreads(); /* S6: M complete */
+    RIC_T(5);
     if (COMPACT && t > 0) issue(t - 1); /* compact layout: Qxu (in the G buffer) has been consumed by steps K and F */
     /* ---- step S: Vxx = (M + M^T)/2 + preg  (src/ddp.cpp:328-333) */
     int bad = 0;
@@ -568,6 +593,7 @@ static __device__ __noinline__ int ric_backward_mma(const Prob& p, double* sm, c
       }
     }
     __syncthreads(); /* S7: Vxx complete */
+    RIC_T(6);
     if (DDP && !rp.is_feasible) { /* Vx += Vxx fs_t  (src/ddp.cpp:336-338) */
       for (int o0 = 0; o0 < NX; o0 += ngrp) {
         const int i = o0 + grp;
@@ -593,6 +619,7 @@ static __device__ __noinline__ int ric_backward_mma(const Prob& p, double* sm, c
         return MIMGPU_STATUS_NONFINITE | (t << 8);
       }
     }
+    RIC_T(7);
   }
   seq = seq0 + (uint32_t)T;
   __syncthreads();
