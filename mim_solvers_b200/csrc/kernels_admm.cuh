@@ -516,6 +516,7 @@ static __device__ __noinline__ void admm_update(const Prob& p, const AdmmScr& sc
   double *xs = ws + W::xs, *us = ws + W::us, *sqx = ws + W::qx, *squ = ws + W::qu, *sd = ws + W::ds, *se1 = sd + ngm,
          *se2 = se1 + ngm;
   WarpStage stg{reinterpret_cast<uint64_t*>(sm + s.wbars) + warp, ws + s.stg, wseq};
+  constexpr bool DEEP = !(NX == 36 && NU == 12);
   const bool check = (iter % q_.rho_update_interval) == 0;
   const bool heur = q_.update_rho_with_heuristic != 0;
   const bool dualg = check && !heur;
@@ -638,6 +639,24 @@ static __device__ __noinline__ void admm_update(const Prob& p, const AdmmScr& sc
         const int rc = valid ? r : 0;
         double a1 = 0.0, a2 = 0.0, b1 = 0.0, b2 = 0.0;
         int j = ph;
+        /* DEEP: eight independent loads in flight per lane where Gx / Gu come from global memory (half as many L2
+         * round trips; same accumulation order as two passes of the four-load loop below).  Measured on B200
+         * (profiles/variants_r02_v4.log): Talos +4 %, constrained LQ nx=64 +10 %, nx=32 +12 %; Solo12, whose G is
+         * staged in shared memory, loses 2 % to the extra code, so 36/12 is compiled without it. */
+        for (; DEEP && !sg && j + 7 * ph_n < NX; j += 8 * ph_n) {
+          const double g0 = Gx[rc + nc * j], g1 = Gx[rc + nc * (j + ph_n)], g2 = Gx[rc + nc * (j + 2 * ph_n)],
+                       g3 = Gx[rc + nc * (j + 3 * ph_n)], g4 = Gx[rc + nc * (j + 4 * ph_n)],
+                       g5 = Gx[rc + nc * (j + 5 * ph_n)], g6 = Gx[rc + nc * (j + 6 * ph_n)],
+                       g7 = Gx[rc + nc * (j + 7 * ph_n)];
+          a1 = fma(g0, xs[j], a1);
+          b1 = fma(g1, xs[j + ph_n], b1);
+          a1 = fma(g2, xs[j + 2 * ph_n], a1);
+          b1 = fma(g3, xs[j + 3 * ph_n], b1);
+          a1 = fma(g4, xs[j + 4 * ph_n], a1);
+          b1 = fma(g5, xs[j + 5 * ph_n], b1);
+          a1 = fma(g6, xs[j + 6 * ph_n], a1);
+          b1 = fma(g7, xs[j + 7 * ph_n], b1);
+        }
         for (; j + 3 * ph_n < NX; j += 4 * ph_n) { /* four independent loads in flight per lane */
           const double g0 = Gx[rc + nc * j], g1 = Gx[rc + nc * (j + ph_n)], g2 = Gx[rc + nc * (j + 2 * ph_n)],
                        g3 = Gx[rc + nc * (j + 3 * ph_n)];
@@ -649,6 +668,20 @@ static __device__ __noinline__ void admm_update(const Prob& p, const AdmmScr& sc
         for (; j < NX; j += ph_n) a1 = fma(Gx[rc + nc * j], xs[j], a1);
         if (Gu) {
           int a = ph;
+          for (; DEEP && !sg && a + 7 * ph_n < NU; a += 8 * ph_n) {
+            const double g0 = Gu[rc + nc * a], g1 = Gu[rc + nc * (a + ph_n)], g2 = Gu[rc + nc * (a + 2 * ph_n)],
+                         g3 = Gu[rc + nc * (a + 3 * ph_n)], g4 = Gu[rc + nc * (a + 4 * ph_n)],
+                         g5 = Gu[rc + nc * (a + 5 * ph_n)], g6 = Gu[rc + nc * (a + 6 * ph_n)],
+                         g7 = Gu[rc + nc * (a + 7 * ph_n)];
+            a2 = fma(g0, us[a], a2);
+            b2 = fma(g1, us[a + ph_n], b2);
+            a2 = fma(g2, us[a + 2 * ph_n], a2);
+            b2 = fma(g3, us[a + 3 * ph_n], b2);
+            a2 = fma(g4, us[a + 4 * ph_n], a2);
+            b2 = fma(g5, us[a + 5 * ph_n], b2);
+            a2 = fma(g6, us[a + 6 * ph_n], a2);
+            b2 = fma(g7, us[a + 7 * ph_n], b2);
+          }
           for (; a + 3 * ph_n < NU; a += 4 * ph_n) {
             const double g0 = Gu[rc + nc * a], g1 = Gu[rc + nc * (a + ph_n)], g2 = Gu[rc + nc * (a + 2 * ph_n)],
                          g3 = Gu[rc + nc * (a + 3 * ph_n)];

@@ -82,6 +82,41 @@ __host__ __device__ inline RicSmem ric_layout(int ng, int ngT, bool with_g, int 
 /* one warp: Cholesky of the NU x NU matrix in sQuu (full symmetric, col-major) -> lower factor
  * in sL (upper part zero), reciprocal pivots in linv.  Eigen::LLT semantics: fails iff a pivot
  * is <= 0 (src/ddp.cpp:413-419).  Returns 1 on failure (uniform over the warp). */
+/* Pivot K of the right-looking factorisation as a template recursion: every index into the per-lane row `a` is a
+ * compile-time constant, so the row stays in registers.  (Written as a `#pragma unroll` loop over k, nvcc kept the
+ * loop rolled for NU = 32 and put `a` into local memory: 58 k cycles per knot in the Talos kernel, 39 % of its
+ * backward sweep -- profiles/ric_step_timing_r02_v5.txt.)  Same operations in the same order as before. */
+template <int K, int NU, int P>
+struct LltStep {
+  static __device__ __forceinline__ void run(double (&a)[P][NU], double* linv, double* col, int lane, int& fail) {
+    /* pivot lives in lane K % 32, register row K / 32 */
+    const double piv = __shfl_sync(0xffffffffu, a[K / 32][K], K % 32);
+    if (piv <= 0.0) fail = 1;
+    const double r = rsqrt(piv);
+    double* cb = col + (K & 1) * NU;
+#pragma unroll
+    for (int rr = 0; rr < P; ++rr) {
+      const int i = lane + 32 * rr;
+      const double lik = (i == K) ? piv * r : a[rr][K] * r;
+      a[rr][K] = lik;
+      if (i < NU) cb[i] = lik;
+    }
+    if (lane == 0) linv[K] = r;
+    __syncwarp();
+#pragma unroll
+    for (int j = K + 1; j < NU; ++j) {
+      const double ljk = cb[j];
+#pragma unroll
+      for (int rr = 0; rr < P; ++rr) a[rr][j] = fma(-a[rr][K], ljk, a[rr][j]);
+    }
+    LltStep<K + 1, NU, P>::run(a, linv, col, lane, fail);
+  }
+};
+template <int NU, int P>
+struct LltStep<NU, NU, P> {
+  static __device__ __forceinline__ void run(double (&)[P][NU], double*, double*, int, int&) {}
+};
+
 template <int NU>
 __device__ __forceinline__ int warp_llt(const double* sQuu, double* sL, double* linv, double* col, int lane) {
   constexpr int P = (NU + 31) / 32;          /* rows per lane */
@@ -93,29 +128,7 @@ __device__ __forceinline__ int warp_llt(const double* sQuu, double* sL, double* 
 #pragma unroll
     for (int j = 0; j < NU; ++j) a[r][j] = (i < NU) ? sQuu[i + NU * j] : 0.0;
   }
-#pragma unroll
-  for (int k = 0; k < NU; ++k) {
-    /* pivot lives in lane k % 32, register row k / 32 */
-    const double piv = __shfl_sync(0xffffffffu, a[k / 32][k], k % 32);
-    if (piv <= 0.0) fail = 1;
-    const double r = rsqrt(piv);
-    double* cb = col + (k & 1) * NU;
-#pragma unroll
-    for (int rr = 0; rr < P; ++rr) {
-      const int i = lane + 32 * rr;
-      const double lik = (i == k) ? piv * r : a[rr][k] * r;
-      a[rr][k] = lik;
-      if (i < NU) cb[i] = lik;
-    }
-    if (lane == 0) linv[k] = r;
-    __syncwarp();
-#pragma unroll
-    for (int j = k + 1; j < NU; ++j) {
-      const double ljk = cb[j];
-#pragma unroll
-      for (int rr = 0; rr < P; ++rr) a[rr][j] = fma(-a[rr][k], ljk, a[rr][j]);
-    }
-  }
+  LltStep<0, NU, P>::run(a, linv, col, lane, fail);
 #pragma unroll
   for (int rr = 0; rr < P; ++rr) {
     const int i = lane + 32 * rr;
@@ -162,6 +175,37 @@ static __device__ long long g_ric_t[16];
 #define RIC_T0() do {} while (0)
 #define RIC_T(slot) do {} while (0)
 #endif
+
+/* Elimination steps of the gain solve (step K of ric_backward_mma) as template recursions, for the same reason as
+ * LltStep: the per-lane slice x[RL] of a right-hand side must stay in registers.  QS lanes share one right-hand side,
+ * lane q owns rows i = q (mod QS). */
+template <int J, int NU, int QS, int RL>
+struct GainSolve {
+  static __device__ __forceinline__ void forward(double (&x)[RL], const double* sL, const double* linv, int lane, int qs) {
+    if constexpr (J < NU) {
+      const double xj = __shfl_sync(0xffffffffu, x[J / QS] * linv[J], (lane & ~(QS - 1)) | (J % QS));
+      if (qs == J % QS) x[J / QS] = xj;
+#pragma unroll
+      for (int r = J / QS; r < RL; ++r) {
+        const int i = r * QS + qs;
+        if (i > J && i < NU) x[r] = fma(-sL[i + NU * J], xj, x[r]);
+      }
+      GainSolve<J + 1, NU, QS, RL>::forward(x, sL, linv, lane, qs);
+    }
+  }
+  static __device__ __forceinline__ void backward(double (&x)[RL], const double* sL, const double* linv, int lane, int qs) {
+    if constexpr (J >= 0) {
+      const double xj = __shfl_sync(0xffffffffu, x[J / QS] * linv[J], (lane & ~(QS - 1)) | (J % QS));
+      if (qs == J % QS) x[J / QS] = xj;
+#pragma unroll
+      for (int r = 0; r <= J / QS; ++r) {
+        const int i = r * QS + qs;
+        if (i < J) x[r] = fma(-sL[J + NU * i], xj, x[r]);
+      }
+      GainSolve<J - 1, NU, QS, RL>::backward(x, sL, linv, lane, qs);
+    }
+  }
+};
 
 /* ------------------------------------------------------------ the backward sweep */
 /* Returns 0 or the status word (uniform over the CTA).  `sm` is the base of a RicSmem
@@ -503,26 +547,8 @@ static __device__ __noinline__ int ric_backward_mma(const Prob& p, double* sm, c
           const int i = r * QS + qs;
           x[r] = (valid && i < NU) ? ((c < NX) ? sQxu[c + NX * i] : sQv[NX + i]) : 0.0;
         }
-#pragma unroll
-        for (int j = 0; j < NU; ++j) { /* L y = b */
-          const double xj = __shfl_sync(0xffffffffu, x[j / QS] * linv[j], (lane & ~(QS - 1)) | (j % QS));
-          if (qs == j % QS) x[j / QS] = xj;
-#pragma unroll
-          for (int r = j / QS; r < RL; ++r) {
-            const int i = r * QS + qs;
-            if (i > j && i < NU) x[r] = fma(-sL[i + NU * j], xj, x[r]);
-          }
-        }
-#pragma unroll
-        for (int j = NU - 1; j >= 0; --j) { /* L^T x = y */
-          const double xj = __shfl_sync(0xffffffffu, x[j / QS] * linv[j], (lane & ~(QS - 1)) | (j % QS));
-          if (qs == j % QS) x[j / QS] = xj;
-#pragma unroll
-          for (int r = 0; r <= j / QS; ++r) {
-            const int i = r * QS + qs;
-            if (i < j) x[r] = fma(-sL[j + NU * i], xj, x[r]);
-          }
-        }
+        GainSolve<0, NU, QS, RL>::forward(x, sL, linv, lane, qs);   /* L y = b */
+        GainSolve<NU - 1, NU, QS, RL>::backward(x, sL, linv, lane, qs); /* L^T x = y */
         if (valid) {
 #pragma unroll
           for (int r = 0; r < RL; ++r) {
