@@ -49,8 +49,14 @@ template <int NX, int NU> struct StreamTune {
 #ifndef MIMGPU_TUNE_C1_MINB
 #define MIMGPU_TUNE_C1_MINB 8
 #endif
+#ifndef MIMGPU_TUNE_C1_MAXT
+#define MIMGPU_TUNE_C1_MAXT 96
+#endif
+#ifndef MIMGPU_C1_SPLIT
+#define MIMGPU_C1_SPLIT 4   /* lanes per dot product of the 12/6 sweeps */
+#endif
 template <> struct StreamTune<36, 12> { static constexpr int MAXT = 192, MINB = MIMGPU_TUNE_C3_MINB; };
-template <> struct StreamTune<12, 6> { static constexpr int MAXT = 96, MINB = MIMGPU_TUNE_C1_MINB; };
+template <> struct StreamTune<12, 6> { static constexpr int MAXT = MIMGPU_TUNE_C1_MAXT, MINB = MIMGPU_TUNE_C1_MINB; };
 template <> struct StreamTune<32, 16> { static constexpr int MAXT = 192, MINB = 2; };
 /* DIRECT shapes: one CTA per SM (the Riccati layout of the full sweeps fills the shared memory) */
 template <> struct StreamTune<64, 32> { static constexpr int MAXT = 384, MINB = 1; };
@@ -156,8 +162,18 @@ k_csqp_direction_stream(KArgs a, StreamKPar kp) {
 }
 
 /* ------------------------------------------------------------------- dispatch */
-#define MIMGPU_STREAM_SHAPES(X) X(12, 6, 4) X(36, 12, 4) X(16, 8, 4) X(8, 4, 4) X(32, 16, 4) X(4, 2, 2) X(6, 2, 2) X(10, 4, 2)
+#define MIMGPU_STREAM_SHAPES(X) X(12, 6, MIMGPU_C1_SPLIT) X(36, 12, 4) X(16, 8, 4) X(8, 4, 4) X(32, 16, 4) X(4, 2, 2) X(6, 2, 2) X(10, 4, 2)
 
+
+/* MIMGPU_STREAM_NT=<32|64|...>: CTA size of the non-DIRECT streaming kernel (tuning switch, read when the
+ * plan is made at mimgpu_create).  The sweeps are written for any multiple of 32 threads and split their dot
+ * products by SPLIT / half-warps, not by the CTA size, so the results do not depend on it. */
+static inline int stream_nt_override(int nt, int maxt) {
+  const char* e = getenv("MIMGPU_STREAM_NT");
+  if (!e) return nt;
+  const int v = atoi(e);
+  return (v >= 32 && v <= maxt && v % 32 == 0) ? v : nt;
+}
 
 template <int NX, int NU, int SPLIT>
 static StreamPlan stream_plan_t(const mimgpu_shape& sh, int stage_fx, int max_smem) {
@@ -173,6 +189,7 @@ static StreamPlan stream_plan_t(const mimgpu_shape& sh, int stage_fx, int max_sm
   if (2 * (NX + ngm) > nt) nt = 2 * (NX + ngm);
   nt = ((nt + 31) / 32) * 32;
   if (nt > StreamTune<NX, NU>::MAXT) nt = StreamTune<NX, NU>::MAXT;
+  nt = stream_nt_override(nt, StreamTune<NX, NU>::MAXT);
   pl.nt = nt;
   const int nvmax = StreamCfg<NX, NU>::VPT * nt;
   if (StreamCfg<NX, NU>::nv_bwd(sh.ng) > nvmax || StreamCfg<NX, NU>::nv_fwd(ngm) > nvmax) return pl;
