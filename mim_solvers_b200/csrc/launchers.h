@@ -13,6 +13,10 @@ namespace mimgpu {
 struct StreamPlan {
   int ok, ns, nt, smem_bytes, generic_total, direct;
 };
+struct RecPlan { /* record-based CSQP kernel of the small shapes (kernels_rec.cuh) */
+  int ok, ns, nt, smem_bytes, generic_total;
+  size_t rec_doubles; /* scratch per problem */
+};
 struct AdmmPlan {
   int ok, nt, smem_bytes, ric_total, nchain, use_mma, stage_g, chain_ns;
 };
@@ -36,6 +40,10 @@ int small_record_offsets_x(const mimgpu_shape& s, int out[16]);
 StreamPlan stream_plan_x(const mimgpu_shape& sh, int stage_fx, int max_smem);
 int stream_csqp_launch_x(const KArgs& a, const mimgpu_csqp_params& q, int with_kkt, const StreamPlan& pl,
                          cudaStream_t st);
+/* record-based CSQP kernel of the small shapes (kernels_rec.cuh); rec = [B][rec_doubles] scratch */
+RecPlan rec_plan_x(const mimgpu_shape& sh, int stage_fx, int max_smem);
+int rec_csqp_launch_x(const KArgs& a, const mimgpu_csqp_params& q, int with_kkt, const RecPlan& pl, double* rec,
+                      cudaStream_t st);
 /* condensed-chain CSQP kernel (kernels_admm.cuh); scratch = {Acl, r, tmp} */
 AdmmPlan admm_plan_x(const mimgpu_shape& sh, int stage_fx, int max_smem);
 int admm_csqp_launch_x(const KArgs& a, const mimgpu_csqp_params& q, int with_kkt, const AdmmPlan& pl,

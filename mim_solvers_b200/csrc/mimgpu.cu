@@ -67,6 +67,9 @@ struct mimgpu_ctx {
   SqpKPar last_sqp{};              /* its parameters, for the on-demand recomputation */
   CtaPlan cplan{};                 /* DMMA CTA-per-problem SQP / FDDP kernel (kernels_cta.cuh) */
   StreamPlan splan{};              /* streaming CSQP kernel (kernels_stream.cuh), ok = 0: not available */
+  RecPlan rplan{};                 /* record-based CSQP kernel of the small shapes (kernels_rec.cuh) */
+  double* rec_scr = nullptr;       /* its knot records [B][T][record]: allocated at the first CSQP call that uses it */
+  bool csqp_rec = false;           /* MIMGPU_CSQP_REC=1: use it */
   AdmmPlan aplan{};                /* condensed-chain CSQP kernel (kernels_admm.cuh): the default CSQP path */
   double* admm_scr[3] = {nullptr, nullptr, nullptr}; /* Acl, r, tmp of the condensed ADMM iterations: allocated at the first CSQP call */
   /* debug / A-B switches, read ONCE at mimgpu_create (never on the hot path) */
@@ -263,6 +266,8 @@ static int configure_launch(mimgpu_ctx* c) {
   c->use_small = small_kernels_configure_x(s);
   c->splan = stream_plan_x(s, stage, max_smem);
   c->aplan = admm_plan_x(s, stage, max_smem);
+  c->rplan = rec_plan_x(s, stage, max_smem);
+  { const char* e = getenv("MIMGPU_CSQP_REC"); c->csqp_rec = e ? atoi(e) != 0 : false; }
   c->cplan = cta_plan_x(s, stage, max_smem);
   c->force_generic = getenv("MIMGPU_FORCE_GENERIC") != nullptr;
   c->csqp_stream = getenv("MIMGPU_CSQP_STREAM") != nullptr;
@@ -345,6 +350,7 @@ void mimgpu_destroy(mimgpu_ctx* c) {
   if (c->pipe_st[0]) cudaStreamDestroy(c->pipe_st[0]);
   if (c->pipe_st[1]) cudaStreamDestroy(c->pipe_st[1]);
   for (int i = 0; i < 3; ++i) cudaFree(c->admm_scr[i]);
+  cudaFree(c->rec_scr);
   cudaFree(c->cost_buf); cudaFree(c->admm_timing); cudaFree(c->model_buf); cudaFree(c->solve_buf);
   cudaFree(c->pack_buf); cudaFree(c->spill_buf); cudaFree(c->in_buf); cudaFree(c->state_buf); cudaFree(c->ibuf); cudaFree(c->reg_buf); cudaFree(c->summary_dev);
   delete c;
@@ -807,6 +813,11 @@ int mimgpu_csqp_direction(mimgpu_ctx* c, const mimgpu_csqp_params* p, int with_k
       }
       return rc;
     }
+  }
+  if (c->rplan.ok && c->csqp_rec && !c->csqp_stream && !c->force_generic && (al & 15) == 0) {
+    if (!c->rec_scr) CU(cudaMalloc(&c->rec_scr, (size_t)c->sh.B * c->rplan.rec_doubles * 8));
+    if (rec_csqp_launch_x(c->k, *p, with_kkt, c->rplan, c->rec_scr, st) == 0)
+      return post_launch(c, "k_csqp_direction_rec");
   }
   if (c->splan.ok && !c->force_generic && (al & 15) == 0 &&
       stream_csqp_launch_x(c->k, *p, with_kkt, c->splan, st) == 0)

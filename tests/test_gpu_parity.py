@@ -301,13 +301,14 @@ def test_gpu_member_flags_do_not_go_stale(eng, oracle_lib):
     assert not g.field("K").any()
 
 
-@pytest.mark.parametrize("switch", ["MIMGPU_CSQP_ADMM", "MIMGPU_CSQP_STREAM"])
+@pytest.mark.parametrize("switch", ["MIMGPU_CSQP_ADMM", "MIMGPU_CSQP_STREAM", "MIMGPU_CSQP_REC"])
 @pytest.mark.parametrize("B,T,nx,nu,ng,ngT,kw", [(6, 40, 12, 6, 3, 3, dict(box_rows=0)), (3, 12, 36, 12, 16, 0, dict(box_rows=12)),
                                                  (3, 10, 16, 8, 24, 16, dict(eq_frac=0.1)), (3, 9, 32, 16, 20, 8, {}),
                                                  (2, 7, 8, 4, 0, 0, {})])
 def test_gpu_csqp_both_kernels(eng, oracle_lib, monkeypatch, switch, B, T, nx, nu, ng, ngT, kw):
-    """The two CSQP kernels (condensed-chain kernels_admm.cuh, sweep-by-sweep kernels_stream.cuh) are
-    dispatched by shape; each is forced here on shapes the other one serves by default."""
+    """The CSQP kernels (condensed-chain kernels_admm.cuh, sweep-by-sweep kernels_stream.cuh, record-based
+    kernels_rec.cuh for nx <= 16) are dispatched by shape; each is forced here on shapes another one serves
+    by default (MIMGPU_CSQP_REC only acts on the shapes the record kernel is compiled for)."""
     from mim_solvers_b200 import _capi
     from mim_solvers_b200.problems import make_random_batch
     monkeypatch.setenv(switch, "1")     # read once, at mimgpu_create
