@@ -51,7 +51,7 @@ __host__ __device__ inline RecSmem rec_smem(int T, int ng, int ngT, int ns, int 
   const int nc = T * ng + ngT;
   int o = 0;
 #define RC_TAKE(n) (o += (((n) + 1) & ~1), o - (((n) + 1) & ~1))
-  s.bars = RC_TAKE(8);
+  s.bars = RC_TAKE(16); /* 8 ring barriers + 2 of the full sweeps */
   s.hdx = RC_TAKE((T + 1) * NX); s.hdu = RC_TAKE(T * NU); s.hy = RC_TAKE(nc); s.hz = RC_TAKE(nc);
   s.hQu = RC_TAKE(T * NU); s.hk = RC_TAKE(T * NU); s.hVx = RC_TAKE((T + 1) * NX);
   s.tmp = RC_TAKE(NX); s.d = RC_TAKE(ngm); s.Qx = RC_TAKE(NX); s.x0 = RC_TAKE(NX); s.x1 = RC_TAKE(NX);
@@ -158,10 +158,16 @@ static __device__ __noinline__ void rec_flush(const Prob& p, const RecSmem& s, b
 /* SolverCSQP::backwardPass_without_rho_update (src/csqp.cpp:1025-1108); the gains k_t = Quu_t^-1 Qu_t
  * (src/csqp.cpp:1096-1097) for all knots after the sweep, one thread per knot. */
 template <int NX, int NU, int SPLIT>
-static __device__ __noinline__ void rec_backward_light(const Prob& p, const RecSmem& s, const RecLay& L, RecPipe& pipe,
+static __device__ __noinline__ void rec_backward_light(const Prob& p, const RecSmem& s_, const RecLay& L_, RecPipe& pipe_,
                                                        double sigma) {
   extern __shared__ __align__(16) double sm_stream[];
   double* sm = sm_stream;
+  /* by-value copies: a struct reached through a reference lives in local memory, and every inline-asm
+   * "memory" clobber (mbarrier, TMA) would force its fields to be re-read there (1081 LDL/STL, 8.9
+   * long-scoreboard stall slots per issue in the first capture) */
+  const RecSmem s = s_;
+  const RecLay L = L_;
+  RecPipe pipe = pipe_;
   const int T = p.T, ng = p.ng, ngT = p.ngT, tid = threadIdx.x, nth = blockDim.x;
   double *tmp = sm + s.tmp, *sd = sm + s.d, *sQx = sm + s.Qx;
   double *hdx = sm + s.hdx, *hdu = sm + s.hdu, *hy = sm + s.hy, *hz = sm + s.hz, *hQu = sm + s.hQu, *hVx = sm + s.hVx,
@@ -272,6 +278,7 @@ static __device__ __noinline__ void rec_backward_light(const Prob& p, const RecS
 #pragma unroll
     for (int i = 0; i < NU; ++i) hk[t * NU + i] = x[i];
   }
+  pipe_ = pipe;
   __syncthreads();
 }
 
@@ -279,10 +286,14 @@ static __device__ __noinline__ void rec_backward_light(const Prob& p, const RecS
 /* SolverCSQP::forwardPass (src/csqp.cpp:630-647) fused with update_lagrangian_parameters
  * (src/csqp.cpp:1196-1340): dx~, du~, z, y, residual norms. */
 template <int NX, int NU, int SPLIT>
-static __device__ __noinline__ void rec_forward_update(const Prob& p, const RecSmem& s, const RecLay& L, RecPipe& pipe,
-                                                       const mimgpu_csqp_params& q_, int iter, AdmmNorms& n) {
+static __device__ __noinline__ void rec_forward_update(const Prob& p, const RecSmem& s_, const RecLay& L_, RecPipe& pipe_,
+                                                       const mimgpu_csqp_params& q_, int iter, AdmmNorms& n_) {
   extern __shared__ __align__(16) double sm_stream[];
   double* sm = sm_stream;
+  const RecSmem s = s_;
+  const RecLay L = L_;
+  RecPipe pipe = pipe_;
+  AdmmNorms n;
   const int T = p.T, ng = p.ng, ngT = p.ngT, tid = threadIdx.x, nth = blockDim.x, lane = tid & 31;
   double *su = sm + s.u, *sdz = sm + s.dz, *sy = sm + s.yy, *red = sm + s.red;
   double *hdx = sm + s.hdx, *hdu = sm + s.hdu, *hy = sm + s.hy, *hz = sm + s.hz, *hk = sm + s.hk;
@@ -437,6 +448,8 @@ static __device__ __noinline__ void rec_forward_update(const Prob& p, const RecS
     n.primal_rel = cta_max(n.primal_rel, red);
     n.dual_rel = cta_max(n.dual_rel, red);
   }
+  n_ = n;
+  pipe_ = pipe;
   __syncthreads();
 }
 
@@ -463,7 +476,7 @@ k_csqp_direction_rec(KArgs a, RecKPar kp) {
   const Smem gs = smem_layout(NX, NU, p.ng, p.ngT, a.stage_fx);
   constexpr bool USE_MMA = (NX % 4 == 0);
   const RicSmem rs = ric_layout<NX, NU>(p.ng, p.ngT, true);
-  uint64_t* ric_bars = reinterpret_cast<uint64_t*>(sm + ss.bars) + 4;
+  uint64_t* ric_bars = reinterpret_cast<uint64_t*>(sm + ss.bars) + 8;
   uint32_t ric_seq = 0u;
   double* rec = kp.rec + (size_t)b * p.T * L.size;
   RecPipe pipe;
@@ -584,10 +597,21 @@ static RecPlan rec_plan_t(const mimgpu_shape& sh, int stage_fx, int max_smem) {
   const RecLay L = rec_layout<NX, NU>(sh.ng);
   pl.rec_doubles = (size_t)sh.T * L.size;
   /* at least four problems per SM, else the streaming kernel (iterates in HBM) serves the shape */
-  for (int ns = 3; ns >= 2; --ns) {
+  int ns_max = 3; /* MIMGPU_REC_NS=2..8: depth of the record ring */
+  if (const char* e = getenv("MIMGPU_REC_NS")) { const int v = atoi(e); if (v >= 2 && v <= 8) ns_max = v; }
+  for (int ns = ns_max; ns >= 2; --ns) {
     const RecSmem ss = rec_smem<NX, NU>(sh.T, sh.ng, sh.ngT, ns, L.size, pl.generic_total);
-    const int bytes = ss.total * 8;
+    int bytes = ss.total * 8;
     if (bytes > max_smem || 4 * (bytes + 1024) > 233472) continue;
+    /* MIMGPU_REC_MAXCTA=n: at most n resident problems per SM (the launch asks for 1/n of the shared memory),
+     * so that the records of the resident wave (n x 148 x T x record) can be sized against the L2 */
+    if (const char* e = getenv("MIMGPU_REC_MAXCTA")) {
+      const int ncta = atoi(e);
+      if (ncta >= 1 && ncta <= 32) {
+        const int want = (233472 / ncta - 1024) & ~15;
+        if (want > bytes && want <= max_smem) bytes = want;
+      }
+    }
     pl.ns = ns; pl.smem_bytes = bytes;
     if (cudaFuncSetAttribute(k_csqp_direction_rec<NX, NU, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) !=
         cudaSuccess) {
