@@ -453,6 +453,293 @@ static __device__ __noinline__ void rec_forward_update(const Prob& p, const RecS
   __syncthreads();
 }
 
+/* ======================================================= one WARP per problem */
+/* The same two sweeps for a 32-thread CTA (MIMGPU_REC_W1): no CTA barrier (a warp barrier orders the
+ * shared-memory hand-offs), one lane per output in the backward mat-vecs (a column of [Fx Fu] / [Gx Gu] is
+ * contiguous in the record: 16-byte loads, no shuffle reduction), Vx carried in a register from knot to
+ * knot.  A third of the instructions of the multi-warp sweeps per knot; sums run over the contraction
+ * index in two interleaved partial sums (the reference: one), inside the 1e-9 bar. */
+template <int NX, int NU>
+static __device__ __noinline__ void rec_backward_light_w1(const Prob& p, const RecSmem& s_, const RecLay& L_, RecPipe& pipe_,
+                                                          double sigma) {
+  static_assert(NX + NU <= 32 && NX % 2 == 0, "one lane per row of [Qx; Qu]");
+  extern __shared__ __align__(16) double sm_stream[];
+  double* sm = sm_stream;
+  const RecSmem s = s_;
+  const RecLay L = L_;
+  RecPipe pipe = pipe_;
+  constexpr int N = NX + NU;
+  const int T = p.T, ng = p.ng, ngT = p.ngT, lane = threadIdx.x;
+  double *tmp = sm + s.tmp, *sd = sm + s.d;
+  double *hdx = sm + s.hdx, *hdu = sm + s.hdu, *hy = sm + s.hy, *hz = sm + s.hz, *hQu = sm + s.hQu, *hVx = sm + s.hVx,
+         *hk = sm + s.hk;
+  __syncwarp();
+  for (int j = 0; j < pipe.ns - 1; ++j)
+    if (T - 1 - j >= 0) pipe.issue(T - 1 - j);
+  /* terminal knot (src/csqp.cpp:1045-1052) */
+  if (ngT) {
+    for (int r = lane; r < ngT; r += 32) {
+      double d = hy[T * ng + r];
+      d -= p.rho[(size_t)T * ng + r] * hz[T * ng + r];
+      sd[r] = d;
+    }
+    __syncwarp();
+  }
+  double vx = 0.0; /* lane i < NX: Vx_{t+1}[i] */
+  if (lane < NX) {
+    double v = p.LxT[lane];
+    v -= sigma * hdx[T * NX + lane];
+    if (ngT) {
+      double acc = 0.0;
+      for (int r = 0; r < ngT; ++r) acc += p.GxT[r + ngT * lane] * sd[r];
+      v += acc;
+    }
+    hVx[T * NX + lane] = v;
+    vx = v;
+  }
+  __syncwarp(); /* sd (terminal) consumed */
+  const bool isx = lane < NX;
+  for (int t = T - 1; t >= 0; --t) {
+    const double* st = sm + s.uni + pipe.acquire_slot() * L.size;
+    /* P0 (src/csqp.cpp:1056-1066) */
+    if (isx) tmp[lane] = st[L.Vf + lane] + vx;
+    for (int r = lane; r < ng; r += 32) {
+      double d = hy[t * ng + r];
+      d -= st[L.rho + r] * hz[t * ng + r];
+      sd[r] = d;
+    }
+    __syncwarp(); /* A: tmp, d visible; every lane is done with knot t+1 */
+    if (t - (pipe.ns - 1) >= 0) pipe.issue(t - (pipe.ns - 1)); /* into the stage of knot t+1 */
+    /* P1: row `lane` of [Qx; Qu] (src/csqp.cpp:1068-1093) */
+    double qv = 0.0;
+    if (lane < N) {
+      const double2* Fc = reinterpret_cast<const double2*>(st + NX * lane); /* [Fx | Fu]: columns of NX */
+      const double2* tv = reinterpret_cast<const double2*>(tmp);
+      double a0 = 0.0, a1 = 0.0;
+#pragma unroll
+      for (int k = 0; k < NX / 2; ++k) {
+        const double2 f = Fc[k], w = tv[k];
+        a0 = fma(f.x, w.x, a0);
+        a1 = fma(f.y, w.y, a1);
+      }
+      const bool gon = ng && (isx ? t > 0 : true);
+      double accg = 0.0;
+      if (gon) {
+        const double* Gc = st + L.Gx + ng * lane; /* [Gx | Gu]: columns of ng */
+        for (int r = 0; r < ng; ++r) accg = fma(Gc[r], sd[r], accg);
+      }
+      double x = st[L.Lx + lane]; /* [Lx | Lu] */
+      x -= sigma * (isx ? hdx[t * NX + lane] : hdu[t * NU + lane - NX]);
+      if (gon) x += accg;
+      x += a0 + a1;
+      qv = x;
+      if (!isx) hQu[t * NU + lane - NX] = x;
+    }
+    __syncwarp(); /* B: Qu visible */
+    /* P2: Vx = Qx - K^T Qu (src/csqp.cpp:1101-1104) */
+    if (isx) {
+      const double* sK = st + L.K;
+      double acc = 0.0;
+#pragma unroll
+      for (int a = 0; a < NU; ++a) acc = fma(sK[a * NX + lane], hQu[t * NU + a], acc);
+      vx = qv - acc;
+      hVx[t * NX + lane] = vx;
+    }
+  }
+  __syncwarp();
+  /* gains (src/csqp.cpp:1096-1097): serial substitution in the reference's order, one lane per knot */
+  for (int t = lane; t < T; t += 32) {
+    const double* Lt = p.L + (size_t)t * NU * NU;
+    double x[NU];
+#pragma unroll
+    for (int i = 0; i < NU; ++i) x[i] = hQu[t * NU + i];
+#pragma unroll
+    for (int i = 0; i < NU; ++i) {
+      double v = x[i];
+#pragma unroll
+      for (int j = 0; j < i; ++j) v -= Lt[i + NU * j] * x[j];
+      x[i] = v / Lt[i + NU * i];
+    }
+#pragma unroll
+    for (int i = NU - 1; i >= 0; --i) {
+      double v = x[i];
+#pragma unroll
+      for (int j = i + 1; j < NU; ++j) v -= Lt[j + NU * i] * x[j];
+      x[i] = v / Lt[i + NU * i];
+    }
+#pragma unroll
+    for (int i = 0; i < NU; ++i) hk[t * NU + i] = x[i];
+  }
+  pipe_ = pipe;
+  __syncwarp();
+}
+
+template <int NX, int NU>
+static __device__ __noinline__ void rec_forward_update_w1(const Prob& p, const RecSmem& s_, const RecLay& L_, RecPipe& pipe_,
+                                                          const mimgpu_csqp_params& q_, int iter, AdmmNorms& n_) {
+  static_assert(NU <= 16, "F1 gives a half-warp lane to every control row");
+  extern __shared__ __align__(16) double sm_stream[];
+  double* sm = sm_stream;
+  const RecSmem s = s_;
+  const RecLay L = L_;
+  RecPipe pipe = pipe_;
+  AdmmNorms n;
+  const int T = p.T, ng = p.ng, ngT = p.ngT, lane = threadIdx.x;
+  double *su = sm + s.u, *sdz = sm + s.dz, *sy = sm + s.yy;
+  double *hdx = sm + s.hdx, *hdu = sm + s.hdu, *hy = sm + s.hy, *hz = sm + s.hz, *hk = sm + s.hk;
+  double* xs[2] = {sm + s.x0, sm + s.x1};
+  const bool check = (iter % q_.rho_update_interval) == 0;
+  const bool heur = q_.update_rho_with_heuristic != 0;
+  const double alpha = q_.alpha;
+  n.primal = n.dual = n.primal_rel = n.dual_rel = -CUDART_INF; /* src/csqp.cpp:1201-1204 */
+  __syncwarp();
+  for (int j = 0; j < pipe.ns - 1; ++j)
+    if (j < T) pipe.issue(j);
+  if (lane < NX) xs[0][lane] = p.dxt[lane];
+  __syncwarp();
+  const int h = lane >> 4, l16 = lane & 15;
+  for (int t = 0; t < T; ++t) {
+    const double* st = sm + s.uni + pipe.acquire_slot() * L.size;
+    const double *sFx = st + L.Fx, *sFu = st + L.Fu, *sK = st + L.K, *sGx = st + L.Gx, *sGu = st + L.Gu;
+    const double* x = xs[t & 1];
+    double* xn = xs[(t + 1) & 1];
+    /* F1: du~ = -k - K dx~ (src/csqp.cpp:636-637): row l16, even / odd contraction index per half-warp */
+    {
+      const bool valid = l16 < NU;
+      const double* Kr = sK + NX * (valid ? l16 : 0);
+      double acc = 0.0;
+#pragma unroll
+      for (int k = 0; k < NX / 2; ++k) acc = fma(Kr[2 * k + h], x[2 * k + h], acc);
+      acc += __shfl_xor_sync(0xffffffffu, acc, 16);
+      if (valid && h == 0) {
+        double u = -hk[t * NU + l16];
+        u -= acc;
+        su[l16] = u;
+        hdu[t * NU + l16] = u;
+      }
+    }
+    if (lane < NX) hdx[t * NX + lane] = x[lane]; /* dx_ := dx~ (src/csqp.cpp:1222-1226, 1241-1242) */
+    __syncwarp(); /* 1: du~ visible; every lane is done with knot t-1 */
+    if (t + pipe.ns - 1 < T) pipe.issue(t + pipe.ns - 1);
+    /* F2: dx~+ = fs+ + Fx dx~ + Fu du~ (src/csqp.cpp:638-644) and the constraint rows of knot t
+     * (src/csqp.cpp:1229-1239); two half-warps share one output */
+    for (int o0 = 0; o0 < NX + ng; o0 += 16) {
+      const int o = o0 + l16;
+      const bool valid = o < NX + ng;
+      const int oc = valid ? o : 0;
+      const bool isx = oc < NX;
+      const int ld = isx ? NX : ng, row = isx ? oc : oc - NX;
+      const double* A1 = (isx ? sFx : sGx) + row;
+      const double* A2 = (isx ? sFu : sGu) + row;
+      double a1 = 0.0, a2 = 0.0;
+#pragma unroll
+      for (int j = 0; j < NX / 2; ++j) a1 = fma(A1[ld * (2 * j + h)], x[2 * j + h], a1);
+#pragma unroll
+      for (int a = 0; a < NU / 2; ++a) a2 = fma(A2[ld * (2 * a + h)], su[2 * a + h], a2);
+      a1 += __shfl_xor_sync(0xffffffffu, a1, 16);
+      a2 += __shfl_xor_sync(0xffffffffu, a2, 16);
+      if (valid && h == 0) {
+        if (isx) {
+          double xv = st[L.fs + o];
+          xv += a1;
+          xv += a2;
+          xn[o] = xv;
+        } else {
+          const int r = o - NX;
+          const double zp = hz[t * ng + r];
+          double c = 0.0;
+          c += a1;
+          c += a2;
+          double zr = alpha * c;
+          zr += (1. - alpha) * zp;
+          const double rho = st[L.rho + r], irho = 1. / rho, yo = hy[t * ng + r];
+          double z = zr + yo * irho;
+          const double lo = st[L.lb + r] - st[L.g + r], hi = st[L.ub + r] - st[L.g + r];
+          z = (z < lo) ? lo : z;
+          z = (hi < z) ? hi : z;
+          const double yn = yo + rho * (zr - z);
+          hz[t * ng + r] = z;
+          hy[t * ng + r] = yn;
+          if (check) {
+            sdz[r] = rho * (z - zp); sy[r] = yn;
+            n.primal = nmax(n.primal, fabs(c - z));
+            n.primal_rel = nmax(n.primal_rel, fabs(c));
+            n.primal_rel = nmax(n.primal_rel, fabs(z));
+            if (heur) {
+              n.dual = nmax(n.dual, fabs(rho * (z - zp)));
+              n.dual_rel = nmax(n.dual_rel, fabs(yn));
+            }
+          }
+        }
+      }
+    }
+    __syncwarp(); /* 2: dx~+ visible */
+    if (check && !heur && ng) { /* F3 (src/csqp.cpp:1259-1278) */
+      for (int o = lane; o < NX + NU; o += 32) {
+        const double* Gc = sGx + ng * o; /* [Gx | Gu]: columns of ng */
+        double a1 = 0.0, a2 = 0.0;
+        for (int r = 0; r < ng; ++r) { a1 = fma(Gc[r], sdz[r], a1); a2 = fma(Gc[r], sy[r], a2); }
+        n.dual = nmax(n.dual, fabs(a1));
+        n.dual_rel = nmax(n.dual_rel, fabs(a2));
+      }
+    }
+  }
+  __syncwarp(); /* F3 of the last knot is done with sdz / sy */
+  /* terminal knot (src/csqp.cpp:1283-1338) */
+  const double* x = xs[T & 1];
+  if (lane < NX) hdx[T * NX + lane] = x[lane];
+  if (ngT) {
+    const size_t o = (size_t)T * ng;
+    for (int r = lane; r < ngT; r += 32) {
+      const double zp = hz[o + r];
+      double acc = 0.0;
+      for (int j = 0; j < NX; ++j) acc += p.GxT[r + ngT * j] * x[j];
+      double c = 0.0;
+      c += acc;
+      double zr = alpha * c;
+      zr += (1. - alpha) * zp;
+      const double rho = p.rho[o + r], irho = 1. / rho, yo = hy[o + r];
+      double z = zr + yo * irho;
+      const double lo = p.glbT[r] - p.gT[r], hi = p.gubT[r] - p.gT[r];
+      z = (z < lo) ? lo : z;
+      z = (hi < z) ? hi : z;
+      const double yn = yo + rho * (zr - z);
+      hz[o + r] = z;
+      hy[o + r] = yn;
+      if (check) {
+        sdz[r] = rho * (z - zp); sy[r] = yn;
+        n.primal = nmax(n.primal, fabs(c - z));
+        n.primal_rel = nmax(n.primal_rel, fabs(c));
+        n.primal_rel = nmax(n.primal_rel, fabs(z));
+        if (heur) {
+          n.dual = nmax(n.dual, fabs(rho * (z - zp)));
+          n.dual_rel = nmax(n.dual_rel, fabs(yn));
+        }
+      }
+    }
+    if (check && !heur) {
+      __syncwarp();
+      for (int j = lane; j < NX; j += 32) {
+        double a1 = 0.0, a2 = 0.0;
+        for (int r = 0; r < ngT; ++r) { a1 += p.GxT[r + ngT * j] * sdz[r]; a2 += p.GxT[r + ngT * j] * sy[r]; }
+        n.dual = nmax(n.dual, fabs(a1));
+        n.dual_rel = nmax(n.dual_rel, fabs(a2));
+      }
+    }
+  }
+  if (check) { /* one warp: shuffles only */
+    for (int o = 16; o; o >>= 1) {
+      n.primal = nmax(n.primal, __shfl_xor_sync(0xffffffffu, n.primal, o));
+      n.dual = nmax(n.dual, __shfl_xor_sync(0xffffffffu, n.dual, o));
+      n.primal_rel = nmax(n.primal_rel, __shfl_xor_sync(0xffffffffu, n.primal_rel, o));
+      n.dual_rel = nmax(n.dual_rel, __shfl_xor_sync(0xffffffffu, n.dual_rel, o));
+    }
+  }
+  n_ = n;
+  pipe_ = pipe;
+  __syncwarp();
+}
+
 /* ------------------------------------------------------------------ the kernel */
 struct RecKPar {
   mimgpu_csqp_params q;
@@ -461,8 +748,11 @@ struct RecKPar {
 };
 
 /* SolverCSQP::computeDirection (src/csqp.cpp:454-517): control flow of k_csqp_direction_stream. */
-template <int NX, int NU, int SPLIT>
-__global__ void __launch_bounds__(StreamTune<NX, NU>::MAXT, StreamTune<NX, NU>::MINB)
+#ifndef MIMGPU_REC_W1_MINB
+#define MIMGPU_REC_W1_MINB 16
+#endif
+template <int NX, int NU, int SPLIT, bool W1 = false> /* W1: one warp per problem (32-thread CTA) */
+__global__ void __launch_bounds__(W1 ? 32 : StreamTune<NX, NU>::MAXT, W1 ? MIMGPU_REC_W1_MINB : StreamTune<NX, NU>::MINB)
 k_csqp_direction_rec(KArgs a, RecKPar kp) {
   static_assert(NX % 2 == 0 && NU % 2 == 0, "TMA bulk copies need 16-byte blocks");
   extern __shared__ __align__(16) double sm_stream[];
@@ -534,10 +824,12 @@ k_csqp_direction_rec(KArgs a, RecKPar kp) {
         rec_load<NX, NU>(p, ss, !in_smem);
         in_smem = true;
       } else {
-        rec_backward_light<NX, NU, SPLIT>(p, ss, L, pipe, q.sigma);
+        if constexpr (W1) rec_backward_light_w1<NX, NU>(p, ss, L, pipe, q.sigma);
+        else rec_backward_light<NX, NU, SPLIT>(p, ss, L, pipe, q.sigma);
       }
       __syncthreads();
-      rec_forward_update<NX, NU, SPLIT>(p, ss, L, pipe, q, it, n);
+      if constexpr (W1) rec_forward_update_w1<NX, NU>(p, ss, L, pipe, q, it, n);
+      else rec_forward_update<NX, NU, SPLIT>(p, ss, L, pipe, q, it, n);
       fwd_ran = true;
       if (it % interval == 0) {
         const double scale = sqrt((n.primal * n.dual_rel) / (n.dual * n.primal_rel));
@@ -590,6 +882,9 @@ static RecPlan rec_plan_t(const mimgpu_shape& sh, int stage_fx, int max_smem) {
   nt = ((nt + 31) / 32) * 32;
   if (nt > StreamTune<NX, NU>::MAXT) nt = StreamTune<NX, NU>::MAXT;
   nt = stream_nt_override(nt, StreamTune<NX, NU>::MAXT);
+  /* MIMGPU_REC_W1=1: one warp per problem */
+  if (const char* e = getenv("MIMGPU_REC_W1")) pl.w1 = (atoi(e) != 0 && NX + NU <= 32 && NU <= 16) ? 1 : 0;
+  if (pl.w1) nt = 32;
   pl.nt = nt;
   /* the full sweeps keep their vector packs: same limit as the streaming kernel */
   const int nvmax = StreamCfg<NX, NU>::VPT * nt;
@@ -613,8 +908,11 @@ static RecPlan rec_plan_t(const mimgpu_shape& sh, int stage_fx, int max_smem) {
       }
     }
     pl.ns = ns; pl.smem_bytes = bytes;
-    if (cudaFuncSetAttribute(k_csqp_direction_rec<NX, NU, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) !=
-        cudaSuccess) {
+    const cudaError_t e1 = pl.w1 ? cudaFuncSetAttribute(k_csqp_direction_rec<NX, NU, SPLIT, true>,
+                                                        cudaFuncAttributeMaxDynamicSharedMemorySize, bytes)
+                                 : cudaFuncSetAttribute(k_csqp_direction_rec<NX, NU, SPLIT, false>,
+                                                        cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e1 != cudaSuccess) {
       cudaGetLastError();
       return pl;
     }
@@ -638,7 +936,8 @@ static inline int rec_csqp_launch(const KArgs& a, const mimgpu_csqp_params& q, i
   kp.q = q; kp.with_kkt = with_kkt; kp.ns = pl.ns; kp.generic_total = pl.generic_total; kp.rec = rec;
 #define X(NX_, NU_, SP_)                                                                        \
   if (a.sh.nx == NX_ && a.sh.nu == NU_) {                                                       \
-    k_csqp_direction_rec<NX_, NU_, SP_><<<a.n_active, pl.nt, pl.smem_bytes, st>>>(a, kp);        \
+    if (pl.w1) k_csqp_direction_rec<NX_, NU_, SP_, true><<<a.n_active, 32, pl.smem_bytes, st>>>(a, kp);   \
+    else k_csqp_direction_rec<NX_, NU_, SP_, false><<<a.n_active, pl.nt, pl.smem_bytes, st>>>(a, kp);   \
     return 0;                                                                                   \
   }
   MIMGPU_REC_SHAPES(X)

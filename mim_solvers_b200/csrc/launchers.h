@@ -14,7 +14,7 @@ struct StreamPlan {
   int ok, ns, nt, smem_bytes, generic_total, direct;
 };
 struct RecPlan { /* record-based CSQP kernel of the small shapes (kernels_rec.cuh) */
-  int ok, ns, nt, smem_bytes, generic_total;
+  int ok, ns, nt, smem_bytes, generic_total, w1;
   size_t rec_doubles; /* scratch per problem */
 };
 struct AdmmPlan {
