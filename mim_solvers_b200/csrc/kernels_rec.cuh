@@ -45,15 +45,19 @@ struct RecSmem {
   int bars, hdx, hdu, hy, hz, hQu, hk, hVx, tmp, d, Qx, x0, x1, u, dz, yy, red, uni, total;
 };
 template <int NX, int NU>
-__host__ __device__ inline RecSmem rec_smem(int T, int ng, int ngT, int ns, int rec_size, int generic_total) {
+__host__ __device__ inline RecSmem rec_smem(int T, int ng, int ngT, int ns, int rec_size, int generic_total,
+                                            bool w1 = false) {
   RecSmem s;
   const int ngm = ng > ngT ? ng : ngT;
   const int nc = T * ng + ngT;
   int o = 0;
 #define RC_TAKE(n) (o += (((n) + 1) & ~1), o - (((n) + 1) & ~1))
   s.bars = RC_TAKE(16); /* 8 ring barriers + 2 of the full sweeps */
-  s.hdx = RC_TAKE((T + 1) * NX); s.hdu = RC_TAKE(T * NU); s.hy = RC_TAKE(nc); s.hz = RC_TAKE(nc);
-  s.hQu = RC_TAKE(T * NU); s.hk = RC_TAKE(T * NU); s.hVx = RC_TAKE((T + 1) * NX);
+  /* one warp per problem: only y, z and k / Qu (one array, solved in place) stay on chip; dx~ du~ stay in the
+   * member arrays (read one knot ahead into a register), Vx is carried in a register -- 13.7 KB instead of
+   * 27.6 KB for UR5 T=40, 15 problems per SM instead of 8 */
+  s.hdx = RC_TAKE(w1 ? 0 : (T + 1) * NX); s.hdu = RC_TAKE(w1 ? 0 : T * NU); s.hy = RC_TAKE(nc); s.hz = RC_TAKE(nc);
+  s.hQu = RC_TAKE(w1 ? 0 : T * NU); s.hk = RC_TAKE(T * NU); s.hVx = RC_TAKE(w1 ? 0 : (T + 1) * NX);
   s.tmp = RC_TAKE(NX); s.d = RC_TAKE(ngm); s.Qx = RC_TAKE(NX); s.x0 = RC_TAKE(NX); s.x1 = RC_TAKE(NX);
   s.u = RC_TAKE(NU); s.dz = RC_TAKE(ngm); s.yy = RC_TAKE(ngm); s.red = RC_TAKE(64);
   s.uni = o; /* union: Riccati layout of the full sweeps | ns record stages */
@@ -151,6 +155,31 @@ static __device__ __noinline__ void rec_flush(const Prob& p, const RecSmem& s, b
   if (all) {
     for (int e = tid; e < (T + 1) * NX; e += nth) p.Vx[e] = sm[s.hVx + e];
     for (int e = tid; e < T * NU; e += nth) { p.Qu[e] = sm[s.hQu + e]; p.kff[e] = sm[s.hk + e]; }
+  }
+}
+
+/* one warp per problem: y, z, k only */
+static __device__ __noinline__ void rec_load_w1(const Prob& p, const RecSmem& s, bool all) {
+  extern __shared__ __align__(16) double sm_stream[];
+  double* sm = sm_stream;
+  const int T = p.T, nc = p.T * p.ng + p.ngT, NU = p.nu, lane = threadIdx.x;
+  for (int e = lane; e < T * NU; e += 32) sm[s.hk + e] = p.kff[e];
+  if (all)
+    for (int e = lane; e < nc; e += 32) { sm[s.hy + e] = p.y[e]; sm[s.hz + e] = p.z[e]; }
+}
+/* final: also k, and dxtilde_ / dutilde_ := dx_ / du_ (what update_lagrangian_parameters leaves, src/csqp.cpp:1222-1226) */
+static __device__ __noinline__ void rec_flush_w1(const Prob& p, const RecSmem& s, bool fwd_ran, bool final, bool with_k) {
+  extern __shared__ __align__(16) double sm_stream[];
+  const double* sm = sm_stream;
+  const int T = p.T, nc = p.T * p.ng + p.ngT, NX = p.nx, NU = p.nu, lane = threadIdx.x;
+  for (int e = lane; e < nc; e += 32) { p.y[e] = sm[s.hy + e]; p.z[e] = sm[s.hz + e]; }
+  if (final) {
+    if (with_k)
+      for (int e = lane; e < T * NU; e += 32) p.kff[e] = sm[s.hk + e];
+    if (fwd_ran) {
+      for (int e = lane; e < (T + 1) * NX; e += 32) p.dxt[e] = p.dx[e];
+      for (int e = lane; e < T * NU; e += 32) p.dut[e] = p.du[e];
+    }
   }
 }
 
@@ -471,8 +500,7 @@ static __device__ __noinline__ void rec_backward_light_w1(const Prob& p, const R
   constexpr int N = NX + NU;
   const int T = p.T, ng = p.ng, ngT = p.ngT, lane = threadIdx.x;
   double *tmp = sm + s.tmp, *sd = sm + s.d;
-  double *hdx = sm + s.hdx, *hdu = sm + s.hdu, *hy = sm + s.hy, *hz = sm + s.hz, *hQu = sm + s.hQu, *hVx = sm + s.hVx,
-         *hk = sm + s.hk;
+  double *hy = sm + s.hy, *hz = sm + s.hz, *hk = sm + s.hk; /* hk holds Qu_t until the gains are solved in place */
   __syncwarp();
   for (int j = 0; j < pipe.ns - 1; ++j)
     if (T - 1 - j >= 0) pipe.issue(T - 1 - j);
@@ -488,18 +516,23 @@ static __device__ __noinline__ void rec_backward_light_w1(const Prob& p, const R
   double vx = 0.0; /* lane i < NX: Vx_{t+1}[i] */
   if (lane < NX) {
     double v = p.LxT[lane];
-    v -= sigma * hdx[T * NX + lane];
+    v -= sigma * p.dx[(size_t)T * NX + lane];
     if (ngT) {
       double acc = 0.0;
       for (int r = 0; r < ngT; ++r) acc += p.GxT[r + ngT * lane] * sd[r];
       v += acc;
     }
-    hVx[T * NX + lane] = v;
+    p.Vx[(size_t)T * NX + lane] = v;
     vx = v;
   }
   __syncwarp(); /* sd (terminal) consumed */
   const bool isx = lane < NX;
+  /* dx~_t / du~_t of the previous forward sweep, read from the member arrays one knot ahead */
+  const double* dsrc = isx ? p.dx + lane : p.du + (lane - NX);
+  const int dstride = isx ? NX : NU;
+  double dcur = (lane < N && T > 0) ? dsrc[(size_t)(T - 1) * dstride] : 0.0;
   for (int t = T - 1; t >= 0; --t) {
+    const double dnext = (lane < N && t > 0) ? dsrc[(size_t)(t - 1) * dstride] : 0.0;
     const double* st = sm + s.uni + pipe.acquire_slot() * L.size;
     /* P0 (src/csqp.cpp:1056-1066) */
     if (isx) tmp[lane] = st[L.Vf + lane] + vx;
@@ -529,21 +562,22 @@ static __device__ __noinline__ void rec_backward_light_w1(const Prob& p, const R
         for (int r = 0; r < ng; ++r) accg = fma(Gc[r], sd[r], accg);
       }
       double x = st[L.Lx + lane]; /* [Lx | Lu] */
-      x -= sigma * (isx ? hdx[t * NX + lane] : hdu[t * NU + lane - NX]);
+      x -= sigma * dcur;
       if (gon) x += accg;
       x += a0 + a1;
       qv = x;
-      if (!isx) hQu[t * NU + lane - NX] = x;
+      if (!isx) { hk[t * NU + lane - NX] = x; p.Qu[(size_t)t * NU + lane - NX] = x; }
     }
+    dcur = dnext;
     __syncwarp(); /* B: Qu visible */
     /* P2: Vx = Qx - K^T Qu (src/csqp.cpp:1101-1104) */
     if (isx) {
       const double* sK = st + L.K;
       double acc = 0.0;
 #pragma unroll
-      for (int a = 0; a < NU; ++a) acc = fma(sK[a * NX + lane], hQu[t * NU + a], acc);
+      for (int a = 0; a < NU; ++a) acc = fma(sK[a * NX + lane], hk[t * NU + a], acc);
       vx = qv - acc;
-      hVx[t * NX + lane] = vx;
+      p.Vx[(size_t)t * NX + lane] = vx;
     }
   }
   __syncwarp();
@@ -552,7 +586,7 @@ static __device__ __noinline__ void rec_backward_light_w1(const Prob& p, const R
     const double* Lt = p.L + (size_t)t * NU * NU;
     double x[NU];
 #pragma unroll
-    for (int i = 0; i < NU; ++i) x[i] = hQu[t * NU + i];
+    for (int i = 0; i < NU; ++i) x[i] = hk[t * NU + i];
 #pragma unroll
     for (int i = 0; i < NU; ++i) {
       double v = x[i];
@@ -586,7 +620,7 @@ static __device__ __noinline__ void rec_forward_update_w1(const Prob& p, const R
   AdmmNorms n;
   const int T = p.T, ng = p.ng, ngT = p.ngT, lane = threadIdx.x;
   double *su = sm + s.u, *sdz = sm + s.dz, *sy = sm + s.yy;
-  double *hdx = sm + s.hdx, *hdu = sm + s.hdu, *hy = sm + s.hy, *hz = sm + s.hz, *hk = sm + s.hk;
+  double *hy = sm + s.hy, *hz = sm + s.hz, *hk = sm + s.hk;
   double* xs[2] = {sm + s.x0, sm + s.x1};
   const bool check = (iter % q_.rho_update_interval) == 0;
   const bool heur = q_.update_rho_with_heuristic != 0;
@@ -615,10 +649,10 @@ static __device__ __noinline__ void rec_forward_update_w1(const Prob& p, const R
         double u = -hk[t * NU + l16];
         u -= acc;
         su[l16] = u;
-        hdu[t * NU + l16] = u;
+        p.du[(size_t)t * NU + l16] = u;
       }
     }
-    if (lane < NX) hdx[t * NX + lane] = x[lane]; /* dx_ := dx~ (src/csqp.cpp:1222-1226, 1241-1242) */
+    if (lane < NX) p.dx[(size_t)t * NX + lane] = x[lane]; /* dx_ := dx~ (src/csqp.cpp:1222-1226, 1241-1242) */
     __syncwarp(); /* 1: du~ visible; every lane is done with knot t-1 */
     if (t + pipe.ns - 1 < T) pipe.issue(t + pipe.ns - 1);
     /* F2: dx~+ = fs+ + Fx dx~ + Fu du~ (src/csqp.cpp:638-644) and the constraint rows of knot t
@@ -687,7 +721,7 @@ static __device__ __noinline__ void rec_forward_update_w1(const Prob& p, const R
   __syncwarp(); /* F3 of the last knot is done with sdz / sy */
   /* terminal knot (src/csqp.cpp:1283-1338) */
   const double* x = xs[T & 1];
-  if (lane < NX) hdx[T * NX + lane] = x[lane];
+  if (lane < NX) p.dx[(size_t)T * NX + lane] = x[lane];
   if (ngT) {
     const size_t o = (size_t)T * ng;
     for (int r = lane; r < ngT; r += 32) {
@@ -760,12 +794,12 @@ k_csqp_direction_rec(KArgs a, RecKPar kp) {
   const int b = a.active ? a.active[blockIdx.x] : (int)blockIdx.x + a.first;
   Prob p = bind(a, b);
   const RecLay L = rec_layout<NX, NU>(p.ng);
-  const RecSmem ss = rec_smem<NX, NU>(p.T, p.ng, p.ngT, kp.ns, L.size, kp.generic_total);
+  const RecSmem ss = rec_smem<NX, NU>(p.T, p.ng, p.ngT, kp.ns, L.size, kp.generic_total, W1);
   double* sm = sm_stream;
   double* gsm = sm + ss.uni;
   const Smem gs = smem_layout(NX, NU, p.ng, p.ngT, a.stage_fx);
   constexpr bool USE_MMA = (NX % 4 == 0);
-  const RicSmem rs = ric_layout<NX, NU>(p.ng, p.ngT, true);
+  const RicSmem rs = ric_layout<NX, NU>(p.ng, p.ngT, true, W1 ? 1 : 2); /* W1: single-buffered full sweeps */
   uint64_t* ric_bars = reinterpret_cast<uint64_t*>(sm + ss.bars) + 8;
   uint32_t ric_seq = 0u;
   double* rec = kp.rec + (size_t)b * p.T * L.size;
@@ -812,7 +846,8 @@ k_csqp_direction_rec(KArgs a, RecKPar kp) {
       if (it % interval == 1 || interval == 1) {
         if (in_smem) { /* the full sweep reads dx_ du_ y z from the member arrays */
           __syncthreads();
-          rec_flush<NX, NU>(p, ss, fwd_ran, false);
+          if constexpr (W1) rec_flush_w1(p, ss, fwd_ran, false, false);
+          else rec_flush<NX, NU>(p, ss, fwd_ran, false);
           __syncthreads();
         }
         if constexpr (USE_MMA) st = ric_backward_mma<MODE_FULL, NX, NU>(p, gsm, rs, rp, ric_bars, ric_seq);
@@ -821,7 +856,8 @@ k_csqp_direction_rec(KArgs a, RecKPar kp) {
         __syncthreads(); /* K, Vxx_fs, k, Vx, Qu of the sweep are visible to the whole CTA */
         rec_build<NX, NU>(p, rec, L, !rec_made);
         rec_made = true;
-        rec_load<NX, NU>(p, ss, !in_smem);
+        if constexpr (W1) rec_load_w1(p, ss, !in_smem);
+        else rec_load<NX, NU>(p, ss, !in_smem);
         in_smem = true;
       } else {
         if constexpr (W1) rec_backward_light_w1<NX, NU>(p, ss, L, pipe, q.sigma);
@@ -852,7 +888,8 @@ k_csqp_direction_rec(KArgs a, RecKPar kp) {
   }
   __syncthreads();
   if (in_smem) { /* after a failed full sweep Vx / Qu / k stay as that sweep left them, as in the streaming kernel */
-    rec_flush<NX, NU>(p, ss, fwd_ran, st == 0);
+    if constexpr (W1) rec_flush_w1(p, ss, fwd_ran, true, st == 0);
+    else rec_flush<NX, NU>(p, ss, fwd_ran, st == 0);
     __syncthreads();
   }
   if (threadIdx.x == 0) {
@@ -870,10 +907,12 @@ k_csqp_direction_rec(KArgs a, RecKPar kp) {
 template <int NX, int NU, int SPLIT>
 static RecPlan rec_plan_t(const mimgpu_shape& sh, int stage_fx, int max_smem) {
   RecPlan pl{};
+  /* MIMGPU_REC_W1=1: one warp per problem */
+  if (const char* e = getenv("MIMGPU_REC_W1")) pl.w1 = (atoi(e) != 0 && NX + NU <= 32 && NU <= 16) ? 1 : 0;
   const Smem gs = smem_layout(NX, NU, sh.ng, sh.ngT, stage_fx);
   pl.generic_total = gs.total;
   if (NX % 4 == 0) {
-    const RicSmem rs = ric_layout<NX, NU>(sh.ng, sh.ngT, true);
+    const RicSmem rs = ric_layout<NX, NU>(sh.ng, sh.ngT, true, pl.w1 ? 1 : 2);
     if (rs.total > pl.generic_total) pl.generic_total = rs.total;
   }
   const int ngm = sh.ng > sh.ngT ? sh.ng : sh.ngT;
@@ -882,8 +921,6 @@ static RecPlan rec_plan_t(const mimgpu_shape& sh, int stage_fx, int max_smem) {
   nt = ((nt + 31) / 32) * 32;
   if (nt > StreamTune<NX, NU>::MAXT) nt = StreamTune<NX, NU>::MAXT;
   nt = stream_nt_override(nt, StreamTune<NX, NU>::MAXT);
-  /* MIMGPU_REC_W1=1: one warp per problem */
-  if (const char* e = getenv("MIMGPU_REC_W1")) pl.w1 = (atoi(e) != 0 && NX + NU <= 32 && NU <= 16) ? 1 : 0;
   if (pl.w1) nt = 32;
   pl.nt = nt;
   /* the full sweeps keep their vector packs: same limit as the streaming kernel */
@@ -895,7 +932,7 @@ static RecPlan rec_plan_t(const mimgpu_shape& sh, int stage_fx, int max_smem) {
   int ns_max = 3; /* MIMGPU_REC_NS=2..8: depth of the record ring */
   if (const char* e = getenv("MIMGPU_REC_NS")) { const int v = atoi(e); if (v >= 2 && v <= 8) ns_max = v; }
   for (int ns = ns_max; ns >= 2; --ns) {
-    const RecSmem ss = rec_smem<NX, NU>(sh.T, sh.ng, sh.ngT, ns, L.size, pl.generic_total);
+    const RecSmem ss = rec_smem<NX, NU>(sh.T, sh.ng, sh.ngT, ns, L.size, pl.generic_total, pl.w1 != 0);
     int bytes = ss.total * 8;
     if (bytes > max_smem || 4 * (bytes + 1024) > 233472) continue;
     /* MIMGPU_REC_MAXCTA=n: at most n resident problems per SM (the launch asks for 1/n of the shared memory),

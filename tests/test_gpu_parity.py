@@ -301,7 +301,8 @@ def test_gpu_member_flags_do_not_go_stale(eng, oracle_lib):
     assert not g.field("K").any()
 
 
-@pytest.mark.parametrize("switch", ["MIMGPU_CSQP_ADMM", "MIMGPU_CSQP_STREAM", "MIMGPU_CSQP_REC"])
+@pytest.mark.parametrize("switch", ["MIMGPU_CSQP_ADMM", "MIMGPU_CSQP_STREAM", "MIMGPU_CSQP_REC", "MIMGPU_REC_W1=0",
+                                    "MIMGPU_REC_W1=1"])
 @pytest.mark.parametrize("B,T,nx,nu,ng,ngT,kw", [(6, 40, 12, 6, 3, 3, dict(box_rows=0)), (3, 12, 36, 12, 16, 0, dict(box_rows=12)),
                                                  (3, 10, 16, 8, 24, 16, dict(eq_frac=0.1)), (3, 9, 32, 16, 20, 8, {}),
                                                  (2, 7, 8, 4, 0, 0, {})])
@@ -311,7 +312,10 @@ def test_gpu_csqp_both_kernels(eng, oracle_lib, monkeypatch, switch, B, T, nx, n
     by default (MIMGPU_CSQP_REC only acts on the shapes the record kernel is compiled for)."""
     from mim_solvers_b200 import _capi
     from mim_solvers_b200.problems import make_random_batch
-    monkeypatch.setenv(switch, "1")     # read once, at mimgpu_create
+    name, _, val = switch.partition("=")
+    monkeypatch.setenv(name, val or "1")     # read once, at mimgpu_create
+    if name == "MIMGPU_REC_W1":
+        monkeypatch.setenv("MIMGPU_CSQP_REC", "1")  # both forms of the record kernel: multi-warp CTA, one warp per problem
     batch = make_random_batch(B, T, nx, nu, ng=ng, ngT=ngT, **kw)
     p = _capi.default_csqp_params(max_qp_iters=120)
     compare_engines_csqp(lambda b: eng(b), lambda b: oracle_lib.Oracle(b), batch, params=p, n_calls=2)
