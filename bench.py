@@ -517,7 +517,7 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--e2e-chunks", type=int, default=8, help="slices of the overlapped host path (SQP)")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--extra", default="C3_solo12_csqp,C5_talos_csqp,C4_clq_nx64",
+    ap.add_argument("--extra", default="C3_solo12_csqp,C5_talos_csqp,C4_clq_nx64,C1_ur5_csqp",
                     help="comma-separated workloads reported in the `workloads` sub-dict of the line")
     ap.add_argument("--extra-steps", type=int, default=5)
     ap.add_argument("--no-extra", action="store_true")

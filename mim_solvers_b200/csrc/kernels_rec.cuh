@@ -17,6 +17,8 @@
  *     memory for the whole ADMM loop and goes to the member arrays before a full sweep reads them and once
  *     at the end: the light iterations issue no other global load or store.
  * Full sweeps, warm start and KKT are the code the streaming kernel runs (kernels_ric.cuh / kernels_generic.cuh).
+ * Default CSQP kernel of the shapes in MIMGPU_REC_SHAPES, in its one-warp-per-problem form (below);
+ * MIMGPU_CSQP_REC=0 / MIMGPU_CSQP_STREAM=1 give the streaming kernel, MIMGPU_REC_W1=0 the multi-warp form.
  *
  * Reference functions restated: backwardPass_without_rho_update (src/csqp.cpp:1025-1108), forwardPass
  * (src/csqp.cpp:630-647), update_lagrangian_parameters (src/csqp.cpp:1196-1340), update_rho_vec /
@@ -905,10 +907,9 @@ k_csqp_direction_rec(KArgs a, RecKPar kp) {
 #define MIMGPU_REC_SHAPES(X) X(12, 6, MIMGPU_C1_SPLIT) X(16, 8, 4) X(8, 4, 4) X(4, 2, 2) X(6, 2, 2) X(10, 4, 2)
 
 template <int NX, int NU, int SPLIT>
-static RecPlan rec_plan_t(const mimgpu_shape& sh, int stage_fx, int max_smem) {
+static RecPlan rec_plan_w(const mimgpu_shape& sh, int stage_fx, int max_smem, int w1) {
   RecPlan pl{};
-  /* MIMGPU_REC_W1=1: one warp per problem */
-  if (const char* e = getenv("MIMGPU_REC_W1")) pl.w1 = (atoi(e) != 0 && NX + NU <= 32 && NU <= 16) ? 1 : 0;
+  pl.w1 = w1;
   const Smem gs = smem_layout(NX, NU, sh.ng, sh.ngT, stage_fx);
   pl.generic_total = gs.total;
   if (NX % 4 == 0) {
@@ -957,6 +958,19 @@ static RecPlan rec_plan_t(const mimgpu_shape& sh, int stage_fx, int max_smem) {
     return pl;
   }
   return pl;
+}
+
+/* one warp per problem (the default; MIMGPU_REC_W1=0 turns it off) when the shape allows it and the vector pack of
+ * the full sweeps fits 32 threads, else the multi-warp CTA */
+template <int NX, int NU, int SPLIT>
+static RecPlan rec_plan_t(const mimgpu_shape& sh, int stage_fx, int max_smem) {
+  bool want_w1 = NX + NU <= 32 && NU <= 16;
+  if (const char* e = getenv("MIMGPU_REC_W1")) want_w1 = want_w1 && atoi(e) != 0;
+  if (want_w1) {
+    const RecPlan pl = rec_plan_w<NX, NU, SPLIT>(sh, stage_fx, max_smem, 1);
+    if (pl.ok) return pl;
+  }
+  return rec_plan_w<NX, NU, SPLIT>(sh, stage_fx, max_smem, 0);
 }
 
 static inline RecPlan rec_plan(const mimgpu_shape& sh, int stage_fx, int max_smem) {

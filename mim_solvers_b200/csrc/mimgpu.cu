@@ -69,7 +69,7 @@ struct mimgpu_ctx {
   StreamPlan splan{};              /* streaming CSQP kernel (kernels_stream.cuh), ok = 0: not available */
   RecPlan rplan{};                 /* record-based CSQP kernel of the small shapes (kernels_rec.cuh) */
   double* rec_scr = nullptr;       /* its knot records [B][T][record]: allocated at the first CSQP call that uses it */
-  bool csqp_rec = false;           /* MIMGPU_CSQP_REC=1: use it */
+  bool csqp_rec = true;            /* MIMGPU_CSQP_REC=0: streaming kernel instead */
   AdmmPlan aplan{};                /* condensed-chain CSQP kernel (kernels_admm.cuh): the default CSQP path */
   double* admm_scr[3] = {nullptr, nullptr, nullptr}; /* Acl, r, tmp of the condensed ADMM iterations: allocated at the first CSQP call */
   /* debug / A-B switches, read ONCE at mimgpu_create (never on the hot path) */
@@ -267,7 +267,7 @@ static int configure_launch(mimgpu_ctx* c) {
   c->splan = stream_plan_x(s, stage, max_smem);
   c->aplan = admm_plan_x(s, stage, max_smem);
   c->rplan = rec_plan_x(s, stage, max_smem);
-  { const char* e = getenv("MIMGPU_CSQP_REC"); c->csqp_rec = e ? atoi(e) != 0 : false; }
+  { const char* e = getenv("MIMGPU_CSQP_REC"); c->csqp_rec = e ? atoi(e) != 0 : true; }
   c->cplan = cta_plan_x(s, stage, max_smem);
   c->force_generic = getenv("MIMGPU_FORCE_GENERIC") != nullptr;
   c->csqp_stream = getenv("MIMGPU_CSQP_STREAM") != nullptr;
@@ -791,7 +791,8 @@ int mimgpu_csqp_direction(mimgpu_ctx* c, const mimgpu_csqp_params* p, int with_k
   const uintptr_t al = (uintptr_t)c->k.Fx | (uintptr_t)c->k.Fu | (uintptr_t)c->k.Gx | (uintptr_t)c->k.Gu;
   /* Measured on B200 (profiles/variants_r02_v1.log): the condensed-chain kernel wins from nx = 32 up (32/16:
    * 13.5 k vs 11.3 k QP/s; Solo12, 48/24, 64/32, Talos); below that a knot is too little work for a
-   * warp-per-knot phase and the sweep-by-sweep streaming kernel stays ahead (UR5: 108 k vs 80 k QP/s). */
+   * warp-per-knot phase: the small shapes go to the record kernel, one warp per problem (UR5: 232 k QP/s against
+   * 108 k of the sweep-by-sweep streaming kernel and 80 k of the condensed one, profiles/rec_w1_r02_v10.log). */
   const bool want_admm = c->csqp_admm || (c->sh.nx >= 32 && !c->csqp_stream) || !c->splan.ok;
   if (c->aplan.ok && !c->force_generic && want_admm && (al & 15) == 0) {
     if (!c->admm_scr[0]) {
