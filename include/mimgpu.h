@@ -303,7 +303,10 @@ int mimgpu_csqp_reset_rho(mimgpu_ctx* ctx, const mimgpu_csqp_params* p,
  * apply_rho_update (:519-582); followed, when with_kkt != 0, by
  * SolverCSQP::checkKKTConditions (:584-628).  The whole ADMM loop runs on the
  * device; qp_iters[b] follows the reference's for-loop semantics
- * (max_qp_iters+1 on exhaustion). */
+ * (max_qp_iters+1 on exhaustion).  The first call allocates the kernel's
+ * per-ctx scratch (cudaMalloc, freed by mimgpu_destroy): knot records
+ * [B][T][nx^2 + 2 nx nu + ng (nx + nu) + 3 nx + nu + 4 ng] for the small shapes,
+ * [B][T][nx^2 + 2 nx] for nx >= 32. */
 int mimgpu_csqp_direction(mimgpu_ctx* ctx, const mimgpu_csqp_params* p,
                           int with_kkt, void* cuda_stream);
 

@@ -61,7 +61,7 @@ __host__ __device__ inline RecSmem rec_smem(int T, int ng, int ngT, int ns, int 
   s.hdx = RC_TAKE(w1 ? 0 : (T + 1) * NX); s.hdu = RC_TAKE(w1 ? 0 : T * NU); s.hy = RC_TAKE(nc); s.hz = RC_TAKE(nc);
   s.hQu = RC_TAKE(w1 ? 0 : T * NU); s.hk = RC_TAKE(T * NU); s.hVx = RC_TAKE(w1 ? 0 : (T + 1) * NX);
   s.tmp = RC_TAKE(NX); s.d = RC_TAKE(ngm); s.Qx = RC_TAKE(NX); s.x0 = RC_TAKE(NX); s.x1 = RC_TAKE(NX);
-  s.u = RC_TAKE(NU); s.dz = RC_TAKE(ngm); s.yy = RC_TAKE(ngm); s.red = RC_TAKE(64);
+  s.u = RC_TAKE(NU); s.dz = RC_TAKE(ngm); s.yy = RC_TAKE(ngm); s.red = RC_TAKE(w1 ? 0 : 64); /* one warp reduces by shuffles */
   s.uni = o; /* union: Riccati layout of the full sweeps | ns record stages */
   const int a = ns * rec_size;
   o += (a > generic_total ? a : generic_total);
@@ -932,6 +932,17 @@ static RecPlan rec_plan_w(const mimgpu_shape& sh, int stage_fx, int max_smem, in
   /* at least four problems per SM, else the streaming kernel (iterates in HBM) serves the shape */
   int ns_max = 3; /* MIMGPU_REC_NS=2..8: depth of the record ring */
   if (const char* e = getenv("MIMGPU_REC_NS")) { const int v = atoi(e); if (v >= 2 && v <= 8) ns_max = v; }
+  /* one warp per problem: resident problems count at least as much as ring depth (measured on UR5: 3 stages x 15 per
+   * SM 232.5 k, 2 stages x 16 per SM 229.8 k, 4 stages x 12 per SM 192 k QP/s), so a shallower ring is taken when it
+   * lets one more problem in */
+  if (pl.w1 && ns_max > 2 && !getenv("MIMGPU_REC_NS")) {
+    auto per_sm = [&](int ns) {
+      const int b = rec_smem<NX, NU>(sh.T, sh.ng, sh.ngT, ns, L.size, pl.generic_total, true).total * 8 + 1024;
+      const int n = 233472 / b;
+      return n > MIMGPU_REC_W1_MINB ? MIMGPU_REC_W1_MINB : n;
+    };
+    while (ns_max > 2 && per_sm(ns_max - 1) > per_sm(ns_max)) --ns_max;
+  }
   for (int ns = ns_max; ns >= 2; --ns) {
     const RecSmem ss = rec_smem<NX, NU>(sh.T, sh.ng, sh.ngT, ns, L.size, pl.generic_total, pl.w1 != 0);
     int bytes = ss.total * 8;

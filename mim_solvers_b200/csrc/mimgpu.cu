@@ -816,8 +816,15 @@ int mimgpu_csqp_direction(mimgpu_ctx* c, const mimgpu_csqp_params* p, int with_k
     }
   }
   if (c->rplan.ok && c->csqp_rec && !c->csqp_stream && !c->force_generic && (al & 15) == 0) {
-    if (!c->rec_scr) CU(cudaMalloc(&c->rec_scr, (size_t)c->sh.B * c->rplan.rec_doubles * 8));
-    if (rec_csqp_launch_x(c->k, *p, with_kkt, c->rplan, c->rec_scr, st) == 0)
+    if (!c->rec_scr && cudaMalloc(&c->rec_scr, (size_t)c->sh.B * c->rplan.rec_doubles * 8) != cudaSuccess) {
+      /* no room for the records: the streaming kernel reads the field-major arrays and needs no scratch */
+      cudaGetLastError();
+      c->rec_scr = nullptr;
+      c->csqp_rec = false;
+      fprintf(stderr, "mimgpu: no memory for the CSQP knot records (%zu MB), using the streaming kernel\n",
+              ((size_t)c->sh.B * c->rplan.rec_doubles * 8) >> 20);
+    }
+    if (c->rec_scr && rec_csqp_launch_x(c->k, *p, with_kkt, c->rplan, c->rec_scr, st) == 0)
       return post_launch(c, "k_csqp_direction_rec");
   }
   if (c->splan.ok && !c->force_generic && (al & 15) == 0 &&
