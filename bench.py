@@ -54,6 +54,8 @@ WORKLOADS = {
     "C4_lq_nx32": dict(solver="sqp", B=4096),
     "C4_clq_nx32": dict(solver="csqp", B=1024),
     "C4_lq_nx16": dict(solver="sqp", B=4096),
+    "C4_clq_nx16": dict(solver="csqp", B=4096),
+    "C4_clq_nx8": dict(solver="csqp", B=4096),
     "C4_lq_nx8": dict(solver="sqp", B=4096),
     "C5_talos_csqp": dict(solver="csqp", B=512),
     "C5_talos_sqp": dict(solver="sqp", B=512),
