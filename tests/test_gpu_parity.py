@@ -56,6 +56,12 @@ CSQP_SHAPES = [  # B, T, nx, nu, ng, ngT, kwargs
     (3, 10, 16, 8, 24, 16, dict(eq_frac=0.1)),
     (2, 5, 64, 32, 96, 64, dict(eq_frac=0.1)),
     (2, 4, 76, 32, 32, 0, dict(box_rows=32)),
+    # the other shapes of the record / streaming CSQP kernels: 8/4 and 4/2 (DMMA full sweeps), 6/2 and 10/4
+    # (nx % 4 != 0: shape-generic full sweeps inside the specialised kernel), odd row counts
+    (5, 9, 8, 4, 12, 8, dict(eq_frac=0.1)),
+    (4, 30, 4, 2, 2, 2, {}),
+    (3, 8, 6, 2, 4, 2, {}),
+    (3, 11, 10, 4, 5, 3, {}),
 ]
 
 
@@ -305,7 +311,7 @@ def test_gpu_member_flags_do_not_go_stale(eng, oracle_lib):
                                     "MIMGPU_REC_W1=1"])
 @pytest.mark.parametrize("B,T,nx,nu,ng,ngT,kw", [(6, 40, 12, 6, 3, 3, dict(box_rows=0)), (3, 12, 36, 12, 16, 0, dict(box_rows=12)),
                                                  (3, 10, 16, 8, 24, 16, dict(eq_frac=0.1)), (3, 9, 32, 16, 20, 8, {}),
-                                                 (2, 7, 8, 4, 0, 0, {})])
+                                                 (2, 7, 8, 4, 0, 0, {}), (3, 8, 6, 2, 4, 2, {}), (3, 11, 10, 4, 5, 3, {})])
 def test_gpu_csqp_both_kernels(eng, oracle_lib, monkeypatch, switch, B, T, nx, nu, ng, ngT, kw):
     """The CSQP kernels (condensed-chain kernels_admm.cuh, sweep-by-sweep kernels_stream.cuh, record-based
     kernels_rec.cuh for nx <= 16) are dispatched by shape; each is forced here on shapes another one serves
