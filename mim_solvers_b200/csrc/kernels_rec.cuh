@@ -4,11 +4,13 @@
  *
  * Why.  On these shapes the sweep-by-sweep streaming kernel (kernels_stream.cuh) moves a knot as five bulk
  * copies of 144 ... 1152 bytes plus ~90 eight-byte asynchronous copies out of eight different arrays, and
- * writes six small vectors back per knot.  Measured on UR5 (profiles/variants_r02_v6_stream_nt.log): 93-108 k
- * QP/s whether a problem has one, two or three warps and whether 8 or 15 problems share an SM -- the kernel
- * is bound by the number and size of its memory requests, not by occupancy, barriers or arithmetic.
+ * writes six small vectors back per knot.  Measured on UR5 (profiles/variants_r02_v6_stream_nt.log,
+ * profiles/ncu_full_r02_v7_csqp_stream_ur5.csv): 93-108 k QP/s whether a problem has one, two or three warps
+ * and whether 8 or 15 problems share an SM, 990 warp instructions per knot step, 1.4 TB/s -- it is bound by
+ * the instructions it spends on moving small pieces, not by occupancy, barriers, DRAM or arithmetic.
  *
- * What changes (arithmetic and its order are those of the streaming sweeps, results are bit-identical):
+ * What changes in the multi-warp form (arithmetic and its order are those of the streaming sweeps, results
+ * are bit-identical; the one-warp form further down keeps less on chip, see there):
  *   - everything a light iteration reads that does NOT change between two rho updates sits in one record
  *     per knot in a scratch array, [Fx | Fu | K | Gx | Gu | Lx | Lu | Vxx_fs | fs_{t+1} | rho | g | lb | ub],
  *     written by the CTA after every full Riccati sweep: a sweep moves a knot with ONE bulk copy (3.2 KB
